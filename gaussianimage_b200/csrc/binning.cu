@@ -1,0 +1,578 @@
+// binning.cu -- tile-intersection counting, prefix sum, emission, onesweep radix sort and tile bin edges.
+//
+// Replaces, for the 2D path, the reference's torch.cumsum + .item() (gsplat/gsplat/utils.py:116-118),
+// map_gaussian_to_intersects (csrc/forward.cu:100-136), torch.sort + torch.gather on 64-bit keys
+// (utils.py:164-165) and get_tile_bin_edges (forward.cu:141-163), including their torch::zeros fills
+// (bindings.cu:289-296, 319-321).
+//
+// Two shapes of the same kernels:
+//   * staged, reference-typed entry points (gi2d_scan_tiles / gi2d_emit_isects / gi2d_sort_isects / gi2d_tile_bins):
+//     int64 keys `(tile << 32) | depth_bits`, int32 values, sizes known on the host -- what the public
+//     gsplat.utils functions return.
+//   * the fused, sync-free chain used by rasterize_gaussians_sum (gi2d_bin_fused): compact uint32 tile keys
+//     (depths are identically 0 in the 2D path, quirk Q2, so only ceil(log2(TX*TY)) key bits are sorted), the
+//     intersection count stays on the device, grids are sized from a host-side capacity, and the last kernel also
+//     packs a 48-byte per-intersection record so that the rasterizers can stage a tile's batch with one bulk TMA copy.
+//
+// The sort is an LSD onesweep radix sort (8-bit digits): one pass = one kernel that ranks a block's keys
+// (warp match_any multisplit, stable), resolves the block's global digit offsets by decoupled look-back over the
+// preceding blocks' digit counts, and scatters.  Stability + ascending-gid emission order gives the per-tile
+// ascending-gid order the reference gets from cub (quirk Q2).  All of this is HBM/L2-bound integer work.
+#include "gi2d_common.cuh"
+
+namespace gi2d {
+
+constexpr int SB = 256;           // threads per block everywhere in this file
+constexpr int RADIX = 256;
+constexpr uint32_t FLAG_AGG = 1u << 30, FLAG_INCL = 2u << 30, VAL_MASK = (1u << 30) - 1;
+constexpr int MAX_PASSES = 8;
+
+// control block (uint32 words), zeroed by one memset per call
+enum { CTL_N = 0, CTL_OVERFLOW = 1, CTL_SCAN_TICKET = 2, CTL_SORT_TICKET = 3 /* ..10 */, CTL_HIST = 16 };
+constexpr int CTL_WORDS = CTL_HIST + MAX_PASSES * RADIX;
+
+struct PassPlan {
+    int npass;
+    int shift[MAX_PASSES];
+    int bits[MAX_PASSES];
+};
+
+__device__ __forceinline__ uint32_t ld_volatile(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
+__device__ __forceinline__ void st_volatile(uint32_t *p, uint32_t v) { *reinterpret_cast<volatile uint32_t *>(p) = v; }
+
+__device__ __forceinline__ int warp_incl_scan(int v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += t;
+    }
+    return v;
+}
+__device__ __forceinline__ int warp_sum(int v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+// Block-wide inclusive scan of one int per thread (SB threads). Returns the inclusive value; *block_total = sum.
+__device__ __forceinline__ int block_incl_scan(int v, int *s_warp /*SB/32*/, int *block_total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = warp_incl_scan(v, lane);
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < SB / 32 ? s_warp[lane] : 0;
+        w = warp_incl_scan(w, lane);
+        if (lane < SB / 32) s_warp[lane] = w;
+    }
+    __syncthreads();
+    if (warp > 0) incl += s_warp[warp - 1];
+    *block_total = s_warp[SB / 32 - 1];
+    return incl;
+}
+
+// Decoupled look-back (single-pass chained scan): executed by warp 0 of block `vbid`; returns the sum of
+// the totals of blocks [0, vbid).  state[] words are FLAG|value (30-bit values), zero = not yet published.
+__device__ __forceinline__ int lookback_exclusive(uint32_t *state, int vbid, int block_total) {
+    const int lane = threadIdx.x & 31;
+    if (lane == 0) st_volatile(state + vbid, (vbid == 0 ? FLAG_INCL : FLAG_AGG) | (uint32_t)block_total);
+    if (vbid == 0) return 0;
+    int excl = 0;
+    int look = vbid - 1;
+    while (true) {
+        const int idx = look - lane;
+        uint32_t w = idx >= 0 ? ld_volatile(state + idx) : FLAG_INCL;
+        while (__any_sync(0xffffffffu, (w >> 30) == 0)) w = idx >= 0 ? ld_volatile(state + idx) : FLAG_INCL;
+        const unsigned incl_mask = __ballot_sync(0xffffffffu, (w & FLAG_INCL) != 0);
+        const int val = (int)(w & VAL_MASK);
+        if (incl_mask) {
+            const int first = __ffs(incl_mask) - 1;
+            excl += warp_sum(lane <= first ? val : 0);
+            break;
+        }
+        excl += warp_sum(val);
+        look -= 32;
+    }
+    if (lane == 0) st_volatile(state + vbid, FLAG_INCL | (uint32_t)(excl + block_total));
+    return excl;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Emission (reference forward.cu:100-136), warp-cooperative: the 32 Gaussians of a warp own one contiguous slot range;
+// lanes walk that range together so stores are coalesced and a Gaussian covering thousands of tiles is spread
+// over the warp.  Slot k of Gaussian g is tile (y0 + k / w, x0 + k % w): tile-row-major like the reference's loop.
+// Slots beyond the recomputed bbox area (inconsistent num_tiles_hit) keep the reference's zero fill.
+// FMT 0: uint32 tile key (+ per-pass digit histogram in shared memory). FMT 1: int64 (tile<<32)|depth_bits.
+template <int FMT>
+__device__ __forceinline__ void warp_emit(int cnt, int off, int x0, int w, int y0, int area, int gid, int dbits,
+                                          int TX, int capacity, void *keys_out, int *vals_out, uint32_t *s_hist,
+                                          const PassPlan &plan) {
+    const int lane = threadIdx.x & 31;
+    const int incl = warp_incl_scan(cnt, lane);
+    const int excl = incl - cnt;
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    const int base = __shfl_sync(0xffffffffu, off, 0);
+    for (int k0 = 0; k0 < total; k0 += 32) {
+        const int k = k0 + lane;
+        const bool active = k < total;
+        int lo = 0, hi = 31;
+#pragma unroll
+        for (int it = 0; it < 5; ++it) {      // smallest lane whose inclusive count exceeds k
+            const int mid = (lo + hi) >> 1;
+            const int v = __shfl_sync(0xffffffffu, incl, mid);
+            if (v > k) hi = mid; else lo = mid + 1;
+        }
+        const int g = min(lo, 31);
+        const int m = k - __shfl_sync(0xffffffffu, excl, g);
+        const int ga = __shfl_sync(0xffffffffu, area, g), gw = __shfl_sync(0xffffffffu, w, g);
+        const int gx0 = __shfl_sync(0xffffffffu, x0, g), gy0 = __shfl_sync(0xffffffffu, y0, g);
+        const int ggid = __shfl_sync(0xffffffffu, gid, g), gdb = __shfl_sync(0xffffffffu, dbits, g);
+        if (!active) continue;
+        int tile = 0, id = 0, db = 0;
+        if (m < ga) {
+            const int row = m / gw;
+            tile = (gy0 + row) * TX + gx0 + (m - row * gw);
+            id = ggid;
+            db = gdb;
+        }
+        const long long pos = (long long)base + k;
+        if (pos < capacity) {
+            if (FMT == 0) {
+                reinterpret_cast<uint32_t *>(keys_out)[pos] = (uint32_t)tile;
+                for (int p = 0; p < plan.npass; ++p)
+                    atomicAdd(&s_hist[p * RADIX + (((uint32_t)tile >> plan.shift[p]) & ((1u << plan.bits[p]) - 1))], 1u);
+            } else {
+                reinterpret_cast<long long *>(keys_out)[pos] = ((long long)tile << 32) | (long long)db;   // sign-extends like forward.cu:125
+            }
+            vals_out[pos] = id;
+        }
+    }
+}
+
+__device__ __forceinline__ void gaussian_bbox(const float *__restrict__ xys, const int *__restrict__ radii, int i, int TX,
+                                              int TY, int &x0, int &w, int &y0, int &area) {
+    x0 = w = y0 = area = 0;
+    const int r = __ldg(radii + i);
+    if (r <= 0) return;                                   // forward.cu:113-114
+    int x1, y1;
+    tile_bbox(__ldg(xys + 2 * (size_t)i), __ldg(xys + 2 * (size_t)i + 1), (float)r, TX, TY, x0, x1, y0, y1);
+    w = x1 - x0;
+    area = max(0, w) * max(0, y1 - y0);
+    if (w <= 0) { w = 1; area = 0; }
+}
+
+// Inclusive int32 scan of num_tiles_hit (utils.py:116) -> cum (may be null) and the total in ctl[CTL_N].
+// FUSED additionally emits the compact (tile, gid) pairs and the digit histograms, and zeroes tile_bins.
+template <bool FUSED>
+__global__ void __launch_bounds__(SB) scan_kernel(int N, const int *__restrict__ num_tiles_hit, int *__restrict__ cum,
+                                                  uint32_t *ctl, uint32_t *scan_state, const float *__restrict__ xys,
+                                                  const int *__restrict__ radii, int TX, int TY, int capacity,
+                                                  uint32_t *keys_out, int *vals_out, PassPlan plan,
+                                                  int *tile_bins_zero, int tile_bins_words) {
+    __shared__ int s_warp[SB / 32];
+    __shared__ int s_bcast[2];
+    __shared__ uint32_t s_hist[FUSED ? MAX_PASSES * RADIX : 1];
+    const int tid = threadIdx.x;
+    if (FUSED) {
+        for (int k = blockIdx.x * SB + tid; k < tile_bins_words; k += gridDim.x * SB) tile_bins_zero[k] = 0;
+        for (int k = tid; k < plan.npass * RADIX; k += SB) s_hist[k] = 0;
+    }
+    if (tid == 0) s_bcast[0] = (int)atomicAdd(ctl + CTL_SCAN_TICKET, 1u);   // virtual block id: look-back order = start order
+    __syncthreads();
+    const int vbid = s_bcast[0];
+    const int i = vbid * SB + tid;
+    const int cnt = i < N ? __ldg(num_tiles_hit + i) : 0;
+    int block_total;
+    const int incl = block_incl_scan(cnt, s_warp, &block_total);
+    if (tid < 32) {
+        const int e = lookback_exclusive(scan_state, vbid, block_total);
+        if (tid == 0) s_bcast[1] = e;
+    }
+    __syncthreads();
+    const int block_excl = s_bcast[1];
+    if (i < N && cum) cum[i] = block_excl + incl;
+    if (vbid == (int)gridDim.x - 1 && tid == 0) {
+        const int total = block_excl + block_total;
+        ctl[CTL_N] = (uint32_t)total;
+        if (FUSED && total > capacity) ctl[CTL_OVERFLOW] = 1u;
+    }
+    if (FUSED) {
+        int x0 = 0, w = 1, y0 = 0, area = 0;
+        if (i < N && cnt > 0) gaussian_bbox(xys, radii, i, TX, TY, x0, w, y0, area);
+        warp_emit<0>(cnt, block_excl + incl - cnt, x0, w, y0, area, i, 0, TX, capacity, keys_out, vals_out, s_hist, plan);
+        __syncthreads();
+        for (int k = tid; k < plan.npass * RADIX; k += SB) {
+            const uint32_t c = s_hist[k];
+            if (c) atomicAdd(ctl + CTL_HIST + k, c);
+        }
+    }
+}
+
+// map_gaussian_to_intersects with reference-typed outputs (int64 keys, int32 ids), offsets from cum_tiles_hit.
+__global__ void __launch_bounds__(SB) emit64_kernel(int N, const float *__restrict__ xys, const float *__restrict__ depths,
+                                                    const int *__restrict__ radii, const int *__restrict__ cum, int TX,
+                                                    int TY, int n_isect, long long *isect_ids, int *gaussian_ids) {
+    const int i = blockIdx.x * SB + threadIdx.x;
+    int cnt = 0, off = 0, x0 = 0, w = 1, y0 = 0, area = 0, db = 0;
+    if (i < N) {
+        const int hi = __ldg(cum + i);
+        off = i == 0 ? 0 : __ldg(cum + i - 1);
+        cnt = max(0, hi - off);
+        gaussian_bbox(xys, radii, i, TX, TY, x0, w, y0, area);
+        db = __float_as_int(__ldg(depths + i));
+    }
+    PassPlan none;
+    none.npass = 0;
+    warp_emit<1>(cnt, off, x0, w, y0, area, i, db, TX, n_isect, isect_ids, gaussian_ids, nullptr, none);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Histogram of all passes' digits at once (staged path; the fused path gets it from the emit kernel).
+template <typename KeyT>
+__global__ void __launch_bounds__(SB) hist_kernel(int n, const KeyT *__restrict__ keys, uint32_t *ctl, PassPlan plan, KeyT flip) {
+    __shared__ uint32_t s_hist[MAX_PASSES * RADIX];
+    for (int k = threadIdx.x; k < plan.npass * RADIX; k += SB) s_hist[k] = 0;
+    __syncthreads();
+    for (int i = blockIdx.x * SB + threadIdx.x; i < n; i += gridDim.x * SB) {
+        const KeyT key = keys[i] ^ flip;
+        for (int p = 0; p < plan.npass; ++p)
+            atomicAdd(&s_hist[p * RADIX + (int)((key >> plan.shift[p]) & (KeyT)((1u << plan.bits[p]) - 1))], 1u);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < plan.npass * RADIX; k += SB) {
+        const uint32_t c = s_hist[k];
+        if (c) atomicAdd(ctl + CTL_HIST + k, c);
+    }
+}
+
+// One onesweep pass. Block tile = SB*ITEMS keys, warp-striped so that (item, lane) order == memory order.
+template <typename KeyT, int ITEMS>
+__global__ void __launch_bounds__(SB) onesweep_kernel(const uint32_t *__restrict__ d_n, int n_host, int capacity,
+                                                      const KeyT *__restrict__ keys_in, const int *__restrict__ vals_in,
+                                                      KeyT *__restrict__ keys_out, int *__restrict__ vals_out,
+                                                      uint32_t *ctl, uint32_t *lookback /* [blocks][RADIX] */, int pass,
+                                                      int shift, int bits, KeyT flip) {
+    constexpr int WARPS = SB / 32, TILE = SB * ITEMS;
+    __shared__ uint32_t s_cnt[WARPS][RADIX];     // per-warp digit counts, then per-warp exclusive offsets
+    __shared__ uint32_t s_base[RADIX];           // global output position of this block's first key of each digit
+    __shared__ uint32_t s_scan[WARPS];
+    __shared__ int s_vbid;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = d_n ? min((int)*d_n, capacity) : n_host;
+    if (tid == 0) s_vbid = (int)atomicAdd(ctl + CTL_SORT_TICKET + pass, 1u);
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) s_cnt[w][tid] = 0;
+    __syncthreads();
+    const int vbid = s_vbid;
+    const int tile_start = vbid * TILE;
+    if (tile_start >= n) return;                 // whole block past the end: nobody looks back at it
+    const uint32_t mask = (1u << bits) - 1;
+
+    KeyT key[ITEMS];
+    int val[ITEMS];
+    uint32_t rank[ITEMS];
+    const int wbase = tile_start + warp * 32 * ITEMS + lane;
+#pragma unroll
+    for (int it = 0; it < ITEMS; ++it) {
+        const int idx = wbase + it * 32;
+        const bool ok = idx < n;
+        key[it] = ok ? keys_in[idx] : (KeyT)0;
+        val[it] = ok ? vals_in[idx] : 0;
+    }
+    const unsigned lt_mask = (1u << lane) - 1;
+#pragma unroll
+    for (int it = 0; it < ITEMS; ++it) {
+        const bool ok = wbase + it * 32 < n;
+        const uint32_t digit = ok ? (uint32_t)(((key[it] ^ flip) >> shift) & (KeyT)mask) : RADIX;   // RADIX = "no key"
+        const unsigned peers = __match_any_sync(0xffffffffu, digit);
+        const uint32_t before = ok ? s_cnt[warp][digit] : 0;
+        __syncwarp();
+        if (ok && (peers & lt_mask) == 0) s_cnt[warp][digit] = before + __popc(peers);   // lowest lane of the group
+        __syncwarp();
+        rank[it] = before + __popc(peers & lt_mask);
+    }
+    __syncthreads();
+    // thread d owns digit d: exclusive scan over warps, publish the block count, look back, add the global digit base
+    {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) {
+            const uint32_t c = s_cnt[w][tid];
+            s_cnt[w][tid] = run;
+            run += c;
+        }
+        uint32_t *my = lookback + (size_t)vbid * RADIX + tid;
+        st_volatile(my, (vbid == 0 ? FLAG_INCL : FLAG_AGG) | run);
+        uint32_t excl = 0;
+        for (int pb = vbid - 1; pb >= 0; --pb) {
+            const uint32_t *p = lookback + (size_t)pb * RADIX + tid;
+            uint32_t w;
+            do { w = ld_volatile(p); } while ((w >> 30) == 0);
+            excl += w & VAL_MASK;
+            if (w & FLAG_INCL) break;
+        }
+        if (vbid > 0) st_volatile(my, FLAG_INCL | (excl + run));
+        // exclusive scan of the global digit histogram of this pass (every block recomputes it: 256 adds)
+        const uint32_t h = ctl[CTL_HIST + pass * RADIX + tid];
+        uint32_t incl = (uint32_t)warp_incl_scan((int)h, lane);
+        if (lane == 31) s_scan[warp] = incl;
+        __syncthreads();
+        uint32_t wprefix = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) wprefix += (w < warp) ? s_scan[w] : 0;
+        s_base[tid] = wprefix + incl - h + excl;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < ITEMS; ++it) {
+        if (wbase + it * 32 < n) {
+            const uint32_t digit = (uint32_t)(((key[it] ^ flip) >> shift) & (KeyT)mask);
+            const uint32_t pos = s_base[digit] + s_cnt[warp][digit] + rank[it];
+            keys_out[pos] = key[it];
+            vals_out[pos] = val[it];
+        }
+    }
+}
+
+// get_tile_bin_edges (forward.cu:141-163) on sorted keys; tile = key >> TSHIFT; rows >= n_bins are skipped (Q4).
+template <typename KeyT, int TSHIFT>
+__global__ void __launch_bounds__(SB) tile_bins_kernel(int n, const KeyT *__restrict__ keys_sorted, int n_bins, int *tile_bins) {
+    for (int i = blockIdx.x * SB + threadIdx.x; i < n; i += gridDim.x * SB) {
+        const int cur = (int)(keys_sorted[i] >> TSHIFT);
+        const bool cur_ok = cur >= 0 && cur < n_bins;
+        if (i == 0 && cur_ok) tile_bins[2 * cur] = 0;
+        if (i == n - 1 && cur_ok) tile_bins[2 * cur + 1] = n;
+        if (i == 0) continue;
+        const int prev = (int)(keys_sorted[i - 1] >> TSHIFT);
+        if (prev != cur) {
+            if (prev >= 0 && prev < n_bins) tile_bins[2 * prev + 1] = i;
+            if (cur_ok) tile_bins[2 * cur] = i;
+        }
+    }
+}
+
+// Fused tail of the sync-free chain: tile bin edges + the packed per-intersection records
+//   rec[i] = { x, y, opacity, conic.x | conic.y, conic.z, r, g | b, gid, 0, 0 }   (3 x float4, 48 B)
+// gathered from the (N,*) tensors in sorted order, so that a tile's batch is one contiguous span for bulk TMA.
+__global__ void __launch_bounds__(SB) bins_pack_kernel(const uint32_t *__restrict__ ctl, int capacity,
+                                                       const uint32_t *__restrict__ keys_sorted,
+                                                       const int *__restrict__ gids_sorted, int n_bins, int *tile_bins,
+                                                       const float *__restrict__ xys, const float *__restrict__ conics,
+                                                       const float *__restrict__ colors, const float *__restrict__ opac,
+                                                       float4 *__restrict__ packed) {
+    const int n = min((int)ctl[CTL_N], capacity);
+    for (int i = blockIdx.x * SB + threadIdx.x; i < n; i += gridDim.x * SB) {
+        const int cur = (int)keys_sorted[i];
+        const bool cur_ok = cur < n_bins;
+        if (i == 0 && cur_ok) tile_bins[2 * cur] = 0;
+        if (i == n - 1 && cur_ok) tile_bins[2 * cur + 1] = n;
+        if (i > 0) {
+            const int prev = (int)keys_sorted[i - 1];
+            if (prev != cur) {
+                if (prev < n_bins) tile_bins[2 * prev + 1] = i;
+                if (cur_ok) tile_bins[2 * cur] = i;
+            }
+        }
+        const int g = gids_sorted[i];
+        const float x = __ldg(xys + 2 * (size_t)g), y = __ldg(xys + 2 * (size_t)g + 1);
+        const float cx = __ldg(conics + 3 * (size_t)g), cy = __ldg(conics + 3 * (size_t)g + 1), cz = __ldg(conics + 3 * (size_t)g + 2);
+        const float r = __ldg(colors + 3 * (size_t)g), gg = __ldg(colors + 3 * (size_t)g + 1), b = __ldg(colors + 3 * (size_t)g + 2);
+        const float o = __ldg(opac + g);
+        packed[3 * (size_t)i + 0] = make_float4(x, y, o, cx);
+        packed[3 * (size_t)i + 1] = make_float4(cy, cz, r, gg);
+        packed[3 * (size_t)i + 2] = make_float4(b, __int_as_float(g), 0.f, 0.f);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+static inline int cuda_status() {
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
+}
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static inline int ceil_log2(long long v) { int b = 0; while ((1ll << b) < v) ++b; return b; }
+
+static PassPlan make_plan(int lo_bit, int hi_bit) {   // sort key bits [lo_bit, hi_bit)
+    PassPlan p;
+    p.npass = 0;
+    for (int s = lo_bit; s < hi_bit && p.npass < MAX_PASSES; s += 8) {
+        p.shift[p.npass] = s;
+        p.bits[p.npass] = (hi_bit - s) < 8 ? (hi_bit - s) : 8;
+        ++p.npass;
+    }
+    return p;
+}
+
+constexpr int SORT_ITEMS = 4;
+constexpr int SORT_TILE = SB * SORT_ITEMS;
+
+struct FusedLayout {          // carve-up of the caller's workspace for gi2d_bin_fused
+    size_t ctl, scan_state, lookback, zero_bytes, keys_a, keys_b, vals_b, total;
+    int scan_blocks, sort_blocks, npass;
+};
+static FusedLayout fused_layout(int N, int T, int capacity) {
+    FusedLayout L;
+    L.npass = make_plan(0, ceil_log2(T > 1 ? T : 2)).npass;
+    L.scan_blocks = (N + SB - 1) / SB;
+    L.sort_blocks = (capacity + SORT_TILE - 1) / SORT_TILE;
+    size_t o = 0;
+    L.ctl = o; o += align_up(sizeof(uint32_t) * CTL_WORDS, 256);
+    L.scan_state = o; o += align_up(sizeof(uint32_t) * (size_t)L.scan_blocks, 256);
+    L.lookback = o; o += align_up(sizeof(uint32_t) * (size_t)L.npass * L.sort_blocks * RADIX, 256);
+    L.zero_bytes = o;
+    L.keys_a = o; o += align_up(sizeof(uint32_t) * (size_t)capacity, 256);
+    L.keys_b = o; o += align_up(sizeof(uint32_t) * (size_t)capacity, 256);
+    L.vals_b = o; o += align_up(sizeof(int) * (size_t)capacity, 256);
+    L.total = o;
+    return L;
+}
+
+}  // namespace gi2d
+
+using namespace gi2d;
+
+extern "C" {
+
+// ---- staged, reference-typed entry points ------------------------------------------------------------------------
+
+size_t gi2d_scan_workspace_bytes(int N) {
+    return align_up(sizeof(uint32_t) * CTL_WORDS, 256) + align_up(sizeof(uint32_t) * (size_t)((N + SB - 1) / SB), 256);
+}
+
+// compute_cumulative_intersects (utils.py:99-118): cum (N,) int32 inclusive; the total is written to *total_out
+// (device or pinned-host-mapped pointer) by a 4-byte async copy on `stream`.
+int gi2d_scan_tiles(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *total_out, void *ws, size_t ws_bytes,
+                    cudaStream_t stream) {
+    if (N <= 0) return GI2D_ERR_INVALID;
+    const size_t need = gi2d_scan_workspace_bytes(N);
+    if (ws_bytes < need) return GI2D_ERR_WORKSPACE;
+    uint32_t *ctl = reinterpret_cast<uint32_t *>(ws);
+    uint32_t *state = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(ws) + align_up(sizeof(uint32_t) * CTL_WORDS, 256));
+    cudaMemsetAsync(ws, 0, need, stream);
+    PassPlan none;
+    none.npass = 0;
+    scan_kernel<false><<<(N + SB - 1) / SB, SB, 0, stream>>>(N, num_tiles_hit, cum_tiles_hit, ctl, state, nullptr, nullptr, 0, 0, 0,
+                                                          nullptr, nullptr, none, nullptr, 0);
+    if (total_out) cudaMemcpyAsync(total_out, ctl + CTL_N, sizeof(int), cudaMemcpyDefault, stream);
+    return cuda_status();
+}
+
+// map_gaussian_to_intersects (utils.py:12-50): every one of the n_isect slots is written.
+int gi2d_emit_isects(int N, const float *xys, const float *depths, const int *radii, const int *cum_tiles_hit, int TX,
+                     int TY, int n_isect, long long *isect_ids, int *gaussian_ids, cudaStream_t stream) {
+    if (N <= 0 || n_isect < 0) return GI2D_ERR_INVALID;
+    if (n_isect == 0) return GI2D_OK;
+    // slots not covered by any Gaussian's range (cum inconsistent with n_isect) keep the reference's zero fill
+    cudaMemsetAsync(isect_ids, 0, sizeof(long long) * (size_t)n_isect, stream);
+    cudaMemsetAsync(gaussian_ids, 0, sizeof(int) * (size_t)n_isect, stream);
+    emit64_kernel<<<(N + SB - 1) / SB, SB, 0, stream>>>(N, xys, depths, radii, cum_tiles_hit, TX, TY, n_isect, isect_ids, gaussian_ids);
+    return cuda_status();
+}
+
+size_t gi2d_sort_workspace_bytes(int n, int begin_bit, int end_bit) {
+    const PassPlan plan = make_plan(begin_bit, end_bit);
+    const int blocks = (n + SORT_TILE - 1) / SORT_TILE;
+    size_t o = align_up(sizeof(uint32_t) * CTL_WORDS, 256);
+    o += align_up(sizeof(uint32_t) * (size_t)plan.npass * blocks * RADIX, 256);
+    o += align_up(sizeof(long long) * (size_t)n, 256) + align_up(sizeof(int) * (size_t)n, 256);
+    return o;
+}
+
+// torch.sort(isect_ids) + gather (utils.py:164-165): stable ascending SIGNED int64 sort of key bits
+// [begin_bit, end_bit) (0..64 sorts everything; 32..32+ceil(log2(tiles)) suffices when all depths are 0).
+int gi2d_sort_isects(int n, const long long *ids_in, const int *gids_in, long long *ids_out, int *gids_out,
+                     int begin_bit, int end_bit, void *ws, size_t ws_bytes, cudaStream_t stream) {
+    if (n < 0 || begin_bit < 0 || end_bit > 64 || begin_bit >= end_bit) return GI2D_ERR_INVALID;
+    if (n == 0) return GI2D_OK;
+    if (ws_bytes < gi2d_sort_workspace_bytes(n, begin_bit, end_bit)) return GI2D_ERR_WORKSPACE;
+    const PassPlan plan = make_plan(begin_bit, end_bit);
+    const int blocks = (n + SORT_TILE - 1) / SORT_TILE;
+    char *base = reinterpret_cast<char *>(ws);
+    size_t o = 0;
+    uint32_t *ctl = reinterpret_cast<uint32_t *>(base + o); o += align_up(sizeof(uint32_t) * CTL_WORDS, 256);
+    uint32_t *lookback = reinterpret_cast<uint32_t *>(base + o); o += align_up(sizeof(uint32_t) * (size_t)plan.npass * blocks * RADIX, 256);
+    const size_t zero_bytes = o;
+    unsigned long long *tmp_k = reinterpret_cast<unsigned long long *>(base + o); o += align_up(sizeof(long long) * (size_t)n, 256);
+    int *tmp_v = reinterpret_cast<int *>(base + o);
+    cudaMemsetAsync(ws, 0, zero_bytes, stream);
+    const unsigned long long flip = end_bit == 64 ? 0x8000000000000000ull : 0ull;   // signed order
+    const unsigned long long *kin = reinterpret_cast<const unsigned long long *>(ids_in);
+    unsigned long long *kout = reinterpret_cast<unsigned long long *>(ids_out);
+    hist_kernel<unsigned long long><<<min(blocks, 1024), SB, 0, stream>>>(n, kin, ctl, plan, flip);
+    // ping-pong so that the last pass lands in (ids_out, gids_out)
+    const unsigned long long *src_k = kin;
+    const int *src_v = gids_in;
+    for (int p = 0; p < plan.npass; ++p) {
+        const bool to_out = ((plan.npass - 1 - p) % 2) == 0;
+        unsigned long long *dst_k = to_out ? kout : tmp_k;
+        int *dst_v = to_out ? gids_out : tmp_v;
+        onesweep_kernel<unsigned long long, SORT_ITEMS><<<blocks, SB, 0, stream>>>(
+            nullptr, n, n, src_k, src_v, dst_k, dst_v, ctl, lookback + (size_t)p * blocks * RADIX, p, plan.shift[p], plan.bits[p], flip);
+        src_k = dst_k;
+        src_v = dst_v;
+    }
+    return cuda_status();
+}
+
+// get_tile_bin_edges (utils.py:53-74): tile_bins (n_bins,2) int32, fully written (zero for empty tiles).
+int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *tile_bins, cudaStream_t stream) {
+    if (n < 0 || n_bins < 0) return GI2D_ERR_INVALID;
+    if (n_bins > 0) cudaMemsetAsync(tile_bins, 0, sizeof(int) * 2 * (size_t)n_bins, stream);
+    if (n == 0) return cuda_status();
+    const int blocks = min((n + SB - 1) / SB, 4096);
+    tile_bins_kernel<long long, 32><<<blocks, SB, 0, stream>>>(n, isect_ids_sorted, n_bins, tile_bins);
+    return cuda_status();
+}
+
+// ---- fused, sync-free chain ---------------------------------------------------------------------------------------
+
+size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity) {
+    return fused_layout(N, TX * TY, capacity).total;
+}
+
+// scan + emit + sort + bin edges + record packing with the intersection count left on the device.
+//   status_out[0] = n_isect (may exceed capacity), status_out[1] = 1 when n_isect > capacity (results truncated).
+//   gids_sorted (capacity,) int32, tile_bins (TX*TY,2) int32, packed (capacity*3) float4.
+// Precondition (2D path): depths are all zero, so the key is the tile id alone.
+int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, const int *num_tiles_hit,
+                   const float *conics, const float *colors, const float *opacities, int capacity, void *ws,
+                   size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed, int *status_out,
+                   cudaStream_t stream) {
+    if (N <= 0 || TX <= 0 || TY <= 0 || capacity <= 0) return GI2D_ERR_INVALID;
+    const int T = TX * TY;
+    const FusedLayout L = fused_layout(N, T, capacity);
+    if (ws_bytes < L.total) return GI2D_ERR_WORKSPACE;
+    char *base = reinterpret_cast<char *>(ws);
+    uint32_t *ctl = reinterpret_cast<uint32_t *>(base + L.ctl);
+    uint32_t *scan_state = reinterpret_cast<uint32_t *>(base + L.scan_state);
+    uint32_t *lookback = reinterpret_cast<uint32_t *>(base + L.lookback);
+    uint32_t *keys_a = reinterpret_cast<uint32_t *>(base + L.keys_a);
+    uint32_t *keys_b = reinterpret_cast<uint32_t *>(base + L.keys_b);
+    int *vals_b = reinterpret_cast<int *>(base + L.vals_b);
+    const PassPlan plan = make_plan(0, ceil_log2(T > 1 ? T : 2));
+
+    cudaMemsetAsync(ws, 0, L.zero_bytes, stream);
+    // values ping-pong between gids_sorted and vals_b; start so that the last pass lands in gids_sorted
+    int *v0 = (plan.npass % 2 == 0) ? gids_sorted : vals_b;
+    uint32_t *k0 = keys_a;
+    scan_kernel<true><<<L.scan_blocks, SB, 0, stream>>>(N, num_tiles_hit, nullptr, ctl, scan_state, xys, radii, TX, TY, capacity, k0,
+                                                       v0, plan, tile_bins, 2 * T);
+    const uint32_t *src_k = k0;
+    const int *src_v = v0;
+    for (int p = 0; p < plan.npass; ++p) {
+        uint32_t *dst_k = (src_k == keys_a) ? keys_b : keys_a;
+        int *dst_v = (src_v == gids_sorted) ? vals_b : gids_sorted;
+        onesweep_kernel<uint32_t, SORT_ITEMS><<<L.sort_blocks, SB, 0, stream>>>(
+            ctl + CTL_N, 0, capacity, src_k, src_v, dst_k, dst_v, ctl, lookback + (size_t)p * L.sort_blocks * RADIX, p,
+            plan.shift[p], plan.bits[p], 0u);
+        src_k = dst_k;
+        src_v = dst_v;
+    }
+    const int pack_blocks = min((capacity + SB - 1) / SB, 148 * 8);
+    bins_pack_kernel<<<pack_blocks, SB, 0, stream>>>(ctl, capacity, src_k, gids_sorted, T, tile_bins, xys, conics, colors, opacities,
+                                                     reinterpret_cast<float4 *>(packed));
+    if (status_out) cudaMemcpyAsync(status_out, ctl, 2 * sizeof(int), cudaMemcpyDeviceToDevice, stream);
+    return cuda_status();
+}
+
+}  // extern "C"

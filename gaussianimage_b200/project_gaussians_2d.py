@@ -1,0 +1,60 @@
+"""project_gaussians_2d: Cholesky-parametrised 2D Gaussians -> pixel centre, conic, radius, tile count.
+
+Mirror of the reference operator gsplat/gsplat/project_gaussians_2d.py:12-141 (same name, arguments, return
+tuple and gradient contract) over the sm_100a kernels of csrc/project.cu.
+"""
+from __future__ import annotations
+
+from typing import Tuple
+
+from torch import Tensor
+from torch.autograd import Function
+
+from . import cuda as _C
+
+
+def _tag_zero_depth(depths: Tensor) -> None:
+    """Both 2D projections write depths == 0 (foward2d.cu:67,122); remember that on the tensor object so that
+    rasterize_gaussians_sum can sort on the tile bits alone (quirk Q2) without inspecting the data."""
+    depths._gi2d_zero_depth_version = depths._version
+
+
+def project_gaussians_2d(
+    means2d: Tensor,
+    L_elements: Tensor,
+    img_height: int,
+    img_width: int,
+    tile_bounds: Tuple[int, int, int],
+    clip_thresh: float = 0.01,
+) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """Returns (xys (N,2), depths (N,), radii (N,) int32, conics (N,3), num_tiles_hit (N,) int32).
+
+    Differentiable w.r.t. means2d and L_elements (through xys and conics); `clip_thresh` is ignored exactly as in
+    the reference kernel (quirk Q11).
+    """
+    return _ProjectGaussians2d.apply(
+        means2d.contiguous(), L_elements.contiguous(), img_height, img_width, tile_bounds, clip_thresh
+    )
+
+
+class _ProjectGaussians2d(Function):
+    @staticmethod
+    def forward(ctx, means2d, L_elements, img_height, img_width, tile_bounds, clip_thresh=0.01):
+        num_points = means2d.shape[-2]
+        xys, depths, radii, conics, num_tiles_hit = _C.project_gaussians_2d_forward(
+            num_points, means2d, L_elements, img_height, img_width, tile_bounds, clip_thresh
+        )
+        ctx.img_height, ctx.img_width, ctx.num_points = img_height, img_width, num_points
+        ctx.save_for_backward(means2d, L_elements, radii, conics)
+        ctx.mark_non_differentiable(radii, num_tiles_hit)
+        _tag_zero_depth(depths)
+        return xys, depths, radii, conics, num_tiles_hit
+
+    @staticmethod
+    def backward(ctx, v_xys, v_depths, v_radii, v_conics, v_num_tiles_hit):
+        means2d, L_elements, radii, conics = ctx.saved_tensors
+        _, v_mean2d, v_L = _C.project_gaussians_2d_backward(
+            ctx.num_points, means2d, L_elements, ctx.img_height, ctx.img_width, radii, conics, v_xys, v_depths, v_conics,
+            want_cov2d=False,   # the reference computes v_cov2d and discards it (project_gaussians_2d.py:114,128-141)
+        )
+        return v_mean2d, v_L, None, None, None, None

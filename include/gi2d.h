@@ -1,0 +1,144 @@
+/*
+ * gi2d.h -- C ABI of libgi2d.so: the B200-native (sm_100a) GaussianImage / gsplat 2D render path.
+ *
+ * Drop-in boundary.  The reference binds its native code with pybind11 (gsplat/gsplat/cuda/csrc/ext.cpp:4-24);
+ * each function below replaces one of those bindings (or a torch op the reference's Python layer calls between
+ * them).  Plain pointers and sizes only -- no torch types.  All pointers are DEVICE pointers unless stated
+ * otherwise; inputs are borrowed, outputs are caller-allocated and FULLY WRITTEN by the call (no pre-zeroing
+ * needed -- the reference's torch::zeros fills are folded into the kernels).  Every call is asynchronous on
+ * `stream` (the reference launches on the legacy default stream, quirk Q9) and returns
+ *   0                       success (launch accepted)
+ *   GI2D_ERR_INVALID   (1)  invalid argument
+ *   GI2D_ERR_WORKSPACE (2)  workspace too small
+ *   1000 + cudaError_t      CUDA launch error
+ * Tiles are 16x16 pixels (reference config.h:1-4; helpers.cuh:36-41 hard-codes 16, quirk Q3):
+ * TX = ceil(W/16), TY = ceil(H/16).  Layouts are the reference's: (N,2)/(N,3) fp32 row-major, images (H,W,3) fp32,
+ * tile_bins (rows,2) int32, keys int64 = (tile << 32) | depth_bits.
+ *
+ * The reference-side binding a maintainer would add (ctypes) is shown in INTEGRATION.md.
+ */
+#ifndef GI2D_H
+#define GI2D_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st *cudaStream_t;
+#endif
+
+#define GI2D_ABI_VERSION 1
+#define GI2D_ERR_INVALID 1
+#define GI2D_ERR_WORKSPACE 2
+#define GI2D_ERR_CUDA_BASE 1000
+
+int gi2d_abi_version(void);
+/* Static description of a status code returned by any function below. */
+const char *gi2d_status_string(int status);
+
+/* ---- projection ------------------------------------------------------------------------------------------- */
+
+/* Replaces project_gaussians_2d_forward (ext.cpp:16 -> bindings.cu:781-839 -> foward2d.cu:12-69).
+ * means2d (N,2) in (-1,1), L (N,3) = (l11,l21,l22).  Outputs: xys (N,2), depths (N) == 0, radii (N) int32,
+ * conics (N,3), num_tiles_hit (N) int32.  `clip_thresh` of the reference is accepted-and-ignored there (Q11),
+ * so it is not part of this signature. */
+int gi2d_project_cholesky_fwd(int N, const float *means2d, const float *L, int H, int W, int TX, int TY, float *xys,
+                              float *depths, int *radii, float *conics, int *num_tiles_hit, cudaStream_t stream);
+
+/* Replaces project_gaussians_2d_scale_rot_forward (ext.cpp:18 -> bindings.cu:841-899 -> foward2d.cu:71-123).
+ * scales2d (N,2), rotation (N,1) radians. */
+int gi2d_project_scale_rot_fwd(int N, const float *means2d, const float *scales2d, const float *rotation, int H, int W,
+                               int TX, int TY, float *xys, float *depths, int *radii, float *conics,
+                               int *num_tiles_hit, cudaStream_t stream);
+
+/* Replaces project_gaussians_2d_backward (ext.cpp:17 -> bindings.cu:902-949 -> backward2d.cu:8-51), including the
+ * reference's doubled off-diagonal term (Q5).  v_cov2d (N,3) may be NULL (the Python layer discards it).
+ * Outputs v_mean2d (N,2), v_L (N,3); rows with radii <= 0 are zero. */
+int gi2d_project_cholesky_bwd(int N, const float *L, int H, int W, const int *radii, const float *conics,
+                              const float *v_xy, const float *v_conic, float *v_cov2d, float *v_mean2d, float *v_L,
+                              cudaStream_t stream);
+
+/* Replaces project_gaussians_2d_scale_rot_backward (ext.cpp:19 -> bindings.cu:951-1004 -> backward2d.cu:53-109).
+ * Outputs v_mean2d (N,2), v_scale (N,2), v_rot (N,1). */
+int gi2d_project_scale_rot_bwd(int N, const float *scales2d, const float *rotation, int H, int W, const int *radii,
+                               const float *conics, const float *v_xy, const float *v_conic, float *v_cov2d,
+                               float *v_mean2d, float *v_scale, float *v_rot, cudaStream_t stream);
+
+/* Replaces compute_cov2d_bounds (ext.cpp:12 -> bindings.cu:21-61).  cov2d (N,3) upper triangle;
+ * conics (N,3), radii (N,1) FLOAT (as in the reference). */
+int gi2d_cov2d_bounds(int N, const float *cov2d, float *conics, float *radii, cudaStream_t stream);
+
+/* ---- binning, staged and reference-typed (the public gsplat.utils functions) ---------------------------------- */
+
+/* Replaces torch.cumsum(int32) of compute_cumulative_intersects (gsplat/gsplat/utils.py:116-118).
+ * cum_tiles_hit (N) int32 inclusive scan; the total is copied (4 bytes, async on `stream`) to *total_out, which may
+ * be a device pointer or a pinned host pointer (the caller synchronises before reading it, like `.item()` does). */
+size_t gi2d_scan_workspace_bytes(int N);
+int gi2d_scan_tiles(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *total_out, void *ws, size_t ws_bytes,
+                    cudaStream_t stream);
+
+/* Replaces map_gaussian_to_intersects (ext.cpp:13 -> bindings.cu:274-313 -> forward.cu:100-136).
+ * isect_ids (n_isect) int64, gaussian_ids (n_isect) int32. */
+int gi2d_emit_isects(int N, const float *xys, const float *depths, const int *radii, const int *cum_tiles_hit, int TX,
+                     int TY, int n_isect, long long *isect_ids, int *gaussian_ids, cudaStream_t stream);
+
+/* Replaces torch.sort + torch.gather of bin_and_sort_gaussians (utils.py:164-165): stable ascending sort of the
+ * int64 keys on bits [begin_bit, end_bit) carrying the int32 ids.  begin=0,end=64 is the full signed sort; in the 2D
+ * path all depth bits are zero (Q2) and begin=32,end=32+ceil(log2(TX*TY)) gives the same result in 2-3 passes. */
+size_t gi2d_sort_workspace_bytes(int n, int begin_bit, int end_bit);
+int gi2d_sort_isects(int n, const long long *ids_in, const int *gids_in, long long *ids_out, int *gids_out,
+                     int begin_bit, int end_bit, void *ws, size_t ws_bytes, cudaStream_t stream);
+
+/* Replaces get_tile_bin_edges (ext.cpp:14 -> bindings.cu:315-330 -> forward.cu:141-163).  tile_bins (n_bins,2);
+ * tile ids >= n_bins are skipped instead of written out of bounds (the reference's Q4 hazard). */
+int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *tile_bins, cudaStream_t stream);
+
+/* ---- binning, fused and sync-free (what rasterize_gaussians_sum runs) ------------------------------------------ */
+
+/* cumsum + map + sort + bin edges (utils.py:116-167) in one asynchronous chain with NO device->host read (the
+ * reference's `.item()`, Q12): the intersection count stays on the device, `capacity` bounds it.
+ *   gids_sorted (capacity) int32, tile_bins (TX*TY,2) int32,
+ *   packed (capacity*12 floats): per sorted intersection {x,y,opacity,conic.x | conic.y,conic.z,r,g | b,gid,0,0}
+ *   status_out (2) int32: [0] = n_isect, [1] = 1 if n_isect > capacity (outputs truncated; retry with more).
+ * Requires all depths == 0 (true for both 2D projections). n_isect < 2^30. */
+size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity);
+int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, const int *num_tiles_hit,
+                   const float *conics, const float *colors, const float *opacities, int capacity, void *ws,
+                   size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed, int *status_out,
+                   cudaStream_t stream);
+
+/* ---- accumulated-sum rasterizer --------------------------------------------------------------------------------- */
+
+/* Replaces rasterize_sum_forward (ext.cpp:22 -> bindings.cu:400-469 -> forward.cu:512-627).
+ * tile_bins must have >= TX*TY rows.  out_img (H,W,3); final_Ts (H,W) == 1 and final_idx (H,W) int32 may both be
+ * NULL.  `background` of the reference is unused by its kernel (Q6) and not part of this signature. */
+int gi2d_raster_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, const int *tile_bins, const float *xys,
+                        const float *conics, const float *colors, const float *opacities, float *out_img,
+                        float *final_Ts, int *final_idx, cudaStream_t stream);
+
+/* Same over the packed records of gi2d_bin_fused (bulk-TMA staging).  If d_status != NULL and d_status[0] == 0 the
+ * image is filled with background[0..2], which is what rasterize_sum.py:121-129 returns for zero intersections. */
+int gi2d_raster_sum_fwd_packed(int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
+                               const int *d_status, const float *background, float *out_img, float *final_Ts,
+                               int *final_idx, cudaStream_t stream);
+
+/* Replaces rasterize_sum_backward (ext.cpp:23 -> bindings.cu:706-779 -> backward.cu:696-862).
+ * v_out (H,W,3).  Outputs v_xy (N,2), v_conic (N,3), v_colors (N,3), v_opacity (N,1) are zeroed by the call.
+ * final_idx is accepted for parity and may be NULL.  fp32 atomic accumulation (order-nondeterministic, as in the
+ * reference). */
+int gi2d_raster_sum_bwd(int N, int TX, int TY, int W, int H, const int *gids_sorted, const int *tile_bins,
+                        const float *xys, const float *conics, const float *colors, const float *opacities,
+                        const int *final_idx, const float *v_out, float *v_xy, float *v_conic, float *v_colors,
+                        float *v_opacity, cudaStream_t stream);
+
+/* Same over the packed records; `grads` is one buffer of 9*N floats: [v_xy | v_conic | v_colors | v_opacity]. */
+int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
+                               const float *v_out, float *grads, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GI2D_H */
