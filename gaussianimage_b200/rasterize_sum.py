@@ -1,0 +1,221 @@
+"""rasterize_gaussians_sum: tile binning + accumulated-sum rasterization, forward and backward.
+
+Mirror of the reference operator gsplat/gsplat/rasterize_sum.py:14-253 (same name, arguments, defaults, return
+value, gradient contract and Python-level errors).  Two execution paths with identical results:
+
+* fast path (depths produced by one of this package's 2D projections, i.e. known to be all zero): the fused,
+  sync-free chain  memset -> scan+emit+histogram -> onesweep passes -> bin edges+record packing -> TMA-staged
+  rasterizer.  The intersection count never leaves the device inside the chain; in the default *strict* mode it is
+  read back once, AFTER everything has been enqueued (so the GPU is never idle waiting for the host, unlike the
+  reference's mid-pipeline `.item()`, quirk Q12), to detect workspace overflow and retry.  While a CUDA graph is
+  being captured, or after `set_sync_free(True)`, no read-back happens at all.
+* general path (arbitrary depths): the reference's own staging -- cumulative intersects (one host read), 64-bit
+  key emit, full 64-bit stable sort, bin edges, index-indirect rasterizer.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+from torch import Tensor
+from torch.autograd import Function
+
+from . import cuda as _C
+from ._lib import check, lib
+from .utils import _depths_known_zero, bin_and_sort_gaussians, compute_cumulative_intersects
+
+_sync_free = os.environ.get("GI2D_SYNC_FREE", "0") == "1"
+_capacity: dict = {}        # (device index, N, TX, TY) -> intersection capacity of the fused workspace
+_last_status: dict = {}     # device index -> (status tensor (2,) int32, capacity) of the most recent fused call
+
+
+def set_sync_free(flag: bool) -> None:
+    """True: never read the intersection count back (graph-capturable, maximum throughput); the caller is expected
+    to call `check_overflow()` now and then.  False (default): strict mode, one read-back at the end of forward."""
+    global _sync_free
+    _sync_free = bool(flag)
+
+
+def check_overflow(device=None) -> int:
+    """Synchronising check of the most recent fused forward on `device`; returns its intersection count and raises
+    if it did not fit the workspace (results of that call were truncated)."""
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    if idx not in _last_status:
+        return 0
+    status, cap, key = _last_status[idx]
+    n, over = status.tolist()
+    if over:
+        _capacity[key] = max(_capacity.get(key, 0), int(n * 1.25) + 1024)
+        raise RuntimeError(f"gi2d: {n} tile intersections exceeded the workspace capacity {cap}; "
+                           "the capacity has been raised, re-run the step")
+    return int(n)
+
+
+def rasterize_gaussians_sum(
+    xys: Tensor,
+    depths: Tensor,
+    radii: Tensor,
+    conics: Tensor,
+    num_tiles_hit: Tensor,
+    colors: Tensor,
+    opacity: Tensor,
+    img_height: int,
+    img_width: int,
+    BLOCK_H: int = 16,
+    BLOCK_W: int = 16,
+    background: Optional[Tensor] = None,
+    return_alpha: Optional[bool] = False,
+) -> Tensor:
+    """Returns out_img (H,W,3) -- or (out_img, out_alpha (H,W)) with return_alpha -- differentiable w.r.t. xys,
+    conics, colors and opacity.  out_img is the plain accumulated sum (no transmittance, no background, Q6);
+    with zero intersections it is `ones * background` as in the reference (rasterize_sum.py:121-129)."""
+    if colors.dtype == torch.uint8:
+        colors = colors.float() / 255           # reference :53-55
+    if background is not None:
+        assert background.shape[0] == colors.shape[-1], (
+            f"incorrect shape of background color tensor, expected shape {colors.shape[-1]}"
+        )
+    else:
+        background = torch.ones(colors.shape[-1], dtype=torch.float32, device=colors.device)
+    if xys.ndimension() != 2 or xys.size(1) != 2:
+        raise ValueError("xys must have dimensions (N, 2)")
+    if colors.ndimension() != 2:
+        raise ValueError("colors must have dimensions (N, D)")
+    return _RasterizeGaussiansSum.apply(
+        xys.contiguous(), depths.contiguous(), radii.contiguous(), conics.contiguous(), num_tiles_hit.contiguous(),
+        colors.contiguous(), opacity.contiguous(), img_height, img_width, BLOCK_H, BLOCK_W, background.contiguous(),
+        return_alpha,
+    )
+
+
+def _align(v: int, a: int = 256) -> int:
+    return (v + a - 1) // a * a
+
+
+class _RasterizeGaussiansSum(Function):
+    @staticmethod
+    def forward(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity, img_height, img_width,
+                BLOCK_H=16, BLOCK_W=16, background=None, return_alpha=False):
+        if (BLOCK_H, BLOCK_W) != (16, 16):
+            raise ValueError("only BLOCK_H = BLOCK_W = 16 is coherent in the reference (helpers.cuh:36-41 divides by a "
+                             "compile-time 16) and supported here")
+        if colors.shape[-1] != 3:
+            # the reference dispatches to _C.nd_rasterize_sum_forward, which is not bound (quirk Q10)
+            raise AttributeError("nd_rasterize_sum_forward: only 3-channel colors are supported "
+                                 "(the reference has no binding for other channel counts either)")
+        H, W = int(img_height), int(img_width)
+        TX, TY = (W + 15) // 16, (H + 15) // 16
+        ctx.H, ctx.W, ctx.TX, ctx.TY = H, W, TX, TY
+        ctx.N = xys.size(0)
+        fast = _depths_known_zero(depths) and xys.is_cuda and xys.dtype == torch.float32
+        ctx.fast = fast
+        if fast:
+            out_img, final_Ts = _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background,
+                                               return_alpha)
+        else:
+            out_img, final_Ts = _forward_staged(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity,
+                                                background)
+        if return_alpha:
+            return out_img, 1 - final_Ts          # reference :181-183 (all zeros unless there were no intersections)
+        return out_img
+
+    @staticmethod
+    def backward(ctx, v_out_img, v_out_alpha=None):
+        N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
+        if ctx.fast:
+            tile_bins, packed = ctx.saved_tensors
+            dev = packed.device
+            v_out = _C._f32(v_out_img.contiguous(), "v_out_img")
+            with torch.cuda.device(dev):
+                grads = torch.empty((9 * N,), dtype=torch.float32, device=dev)
+                check(lib().gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(),
+                                                       v_out.data_ptr(), grads.data_ptr(), _C._stream(dev)),
+                      "rasterize_sum_backward")
+            v_xy = grads[: 2 * N].view(N, 2)
+            v_conic = grads[2 * N: 5 * N].view(N, 3)
+            v_colors = grads[5 * N: 8 * N].view(N, 3)
+            v_opacity = grads[8 * N:].view(N, 1)
+        else:
+            gids_sorted, tile_bins, xys, conics, colors, opacity, background, final_Ts, final_idx = ctx.saved_tensors
+            if ctx.num_intersects < 1:          # reference :209-213
+                v_xy, v_conic = torch.zeros_like(xys), torch.zeros_like(conics)
+                v_colors, v_opacity = torch.zeros_like(colors), torch.zeros_like(opacity)
+            else:
+                if v_out_alpha is None:
+                    v_out_alpha = torch.zeros_like(v_out_img[..., 0])
+                v_xy, v_conic, v_colors, v_opacity = _C.rasterize_sum_backward(
+                    H, W, 16, 16, gids_sorted, tile_bins, xys, conics, colors, opacity, background, final_Ts, final_idx,
+                    v_out_img, v_out_alpha)
+        v_opacity = v_opacity.view(ctx.opacity_shape)
+        return (v_xy, None, None, v_conic, None, v_colors, v_opacity, None, None, None, None, None, None)
+
+
+def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background, want_aux):
+    N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
+    dev = xys.device
+    L = lib()
+    xys, conics, colors = _C._f32(xys, "xys"), _C._f32(conics, "conics"), _C._f32(colors, "colors")
+    opacity, background = _C._f32(opacity, "opacity"), _C._f32(background.to(dev), "background")
+    radii, nth = _C._i32(radii, "radii"), _C._i32(num_tiles_hit, "num_tiles_hit")
+    ctx.opacity_shape = opacity.shape
+    key = (dev.index, N, TX, TY)
+    capturing = torch.cuda.is_current_stream_capturing()
+    strict = not (_sync_free or capturing)
+    with torch.cuda.device(dev):
+        stream = _C._stream(dev)
+        while True:
+            cap = _capacity.get(key)
+            if cap is None:
+                cap = _capacity[key] = max(4 * N, 1 << 14)
+            ws_bytes = L.gi2d_bin_fused_workspace_bytes(N, TX, TY, cap)
+            # one allocation: [workspace | gids_sorted | status]; tile_bins and packed are kept for backward
+            o_gids = _align(ws_bytes)
+            o_status = o_gids + _align(4 * cap)
+            scratch = torch.empty((o_status + 256,), dtype=torch.uint8, device=dev)
+            tile_bins = torch.empty((TX * TY, 2), dtype=torch.int32, device=dev)
+            packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
+            base = scratch.data_ptr()
+            check(L.gi2d_bin_fused(N, TX, TY, xys.data_ptr(), radii.data_ptr(), nth.data_ptr(), conics.data_ptr(),
+                                   colors.data_ptr(), opacity.data_ptr(), cap, base, ws_bytes, base + o_gids,
+                                   tile_bins.data_ptr(), packed.data_ptr(), base + o_status, stream), "bin_fused")
+            out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+            final_Ts = torch.empty((H, W), dtype=torch.float32, device=dev) if want_aux else None
+            final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if want_aux else None
+            check(L.gi2d_raster_sum_fwd_packed(TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(), base + o_status,
+                                               background.data_ptr(), out_img.data_ptr(), _C._p(final_Ts),
+                                               _C._p(final_idx), stream), "rasterize_sum_forward")
+            status = scratch[o_status:o_status + 8].view(torch.int32)
+            _last_status[dev.index] = (status, cap, key)
+            if not strict:
+                break
+            n, over = status.tolist()              # the single device->host read, after everything is enqueued
+            if not over:
+                ctx.num_intersects = n
+                break
+            _capacity[key] = int(n * 1.25) + 1024  # truncated: grow and redo
+    ctx.save_for_backward(tile_bins, packed)
+    return out_img, final_Ts
+
+
+def _forward_staged(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity, background):
+    """The reference's own sequence (rasterize_sum.py:109-179) over the staged entry points."""
+    N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
+    ctx.opacity_shape = opacity.shape
+    tile_bounds = (TX, TY, 1)
+    num_intersects, cum_tiles_hit = compute_cumulative_intersects(num_tiles_hit)
+    dev = xys.device
+    if num_intersects < 1:
+        out_img = torch.ones(H, W, colors.shape[-1], device=dev) * background
+        gids_sorted = torch.zeros(0, 1, device=dev)
+        tile_bins = torch.zeros(0, 2, device=dev)
+        final_Ts = torch.zeros(H, W, device=dev)
+        final_idx = torch.zeros(H, W, device=dev)
+    else:
+        _, _, _, gids_sorted, tile_bins = bin_and_sort_gaussians(N, num_intersects, xys, depths, radii, cum_tiles_hit,
+                                                                 tile_bounds)
+        out_img, final_Ts, final_idx = _C.rasterize_sum_forward(tile_bounds, (16, 16, 1), (W, H, 1), gids_sorted, tile_bins,
+                                                                xys, conics, colors, opacity, background)
+    ctx.num_intersects = num_intersects
+    ctx.save_for_backward(gids_sorted, tile_bins, xys, conics, colors, opacity, background, final_Ts, final_idx)
+    return out_img, final_Ts

@@ -57,7 +57,7 @@ def project_gaussians_2d(means2d, L, H, W, tile_bounds_=None):
     """foward2d.cu:12-69 -> (xys, depths, radii, conics, num_tiles_hit)."""
     means2d, L = _c(means2d, _f), _c(L, _f)
     N = means2d.shape[0]
-    TX, TY = tile_bounds_[:2] if tile_bounds_ is not None else tile_bounds(H, W)
+    TX, TY = (int(tile_bounds_[0]), int(tile_bounds_[1])) if tile_bounds_ is not None else tile_bounds(H, W)
     xys, depths = np.zeros((N, 2), _f), np.zeros(N, _f)
     radii, conics, nth = np.zeros(N, _i), np.zeros((N, 3), _f), np.zeros(N, _i)
     lib().gi2d_oracle_project_cholesky_fwd(N, _p(means2d), _p(L), H, W, TX, TY, _p(xys), _p(depths), _p(radii),
@@ -69,7 +69,7 @@ def project_gaussians_2d_scale_rot(means2d, scales, rot, H, W, tile_bounds_=None
     """foward2d.cu:71-123."""
     means2d, scales, rot = _c(means2d, _f), _c(scales, _f), _c(rot, _f).reshape(-1)
     N = means2d.shape[0]
-    TX, TY = tile_bounds_[:2] if tile_bounds_ is not None else tile_bounds(H, W)
+    TX, TY = (int(tile_bounds_[0]), int(tile_bounds_[1])) if tile_bounds_ is not None else tile_bounds(H, W)
     xys, depths = np.zeros((N, 2), _f), np.zeros(N, _f)
     radii, conics, nth = np.zeros(N, _i), np.zeros((N, 3), _f), np.zeros(N, _i)
     lib().gi2d_oracle_project_scale_rot_fwd(N, _p(means2d), _p(scales), _p(rot), H, W, TX, TY, _p(xys), _p(depths),
@@ -97,9 +97,10 @@ def compute_cumulative_intersects(num_tiles_hit):
 def map_gaussian_to_intersects(num_points, num_intersects, xys, depths, radii, cum_tiles_hit, tile_bounds_):
     """forward.cu:100-136 -> (isect_ids int64, gaussian_ids int32)."""
     xys, depths, radii, cum = _c(xys, _f), _c(depths, _f), _c(radii, _i), _c(cum_tiles_hit, _i)
+    num_intersects = int(num_intersects)
     ids, gids = np.zeros(num_intersects, np.int64), np.zeros(num_intersects, _i)
-    lib().gi2d_oracle_map_intersects(num_points, _p(xys), _p(depths), _p(radii), _p(cum), tile_bounds_[0],
-                                     tile_bounds_[1], _p(ids), _p(gids))
+    lib().gi2d_oracle_map_intersects(int(num_points), _p(xys), _p(depths), _p(radii), _p(cum), int(tile_bounds_[0]),
+                                     int(tile_bounds_[1]), _p(ids), _p(gids))
     return ids, gids
 
 
@@ -114,7 +115,8 @@ def sort_intersects(isect_ids, gaussian_ids):
 def get_tile_bin_edges(num_intersects, isect_ids_sorted, n_bins=None):
     """forward.cu:141-163; n_bins rows (default num_intersects like bindings.cu:319-321)."""
     ids = _c(isect_ids_sorted, np.int64)
-    n_bins = num_intersects if n_bins is None else n_bins
+    num_intersects = int(num_intersects)
+    n_bins = num_intersects if n_bins is None else int(n_bins)
     bins = np.zeros((n_bins, 2), _i)
     lib().gi2d_oracle_tile_bin_edges(num_intersects, _p(ids), n_bins, _p(bins))
     return bins
@@ -124,7 +126,7 @@ def bin_and_sort_gaussians(num_points, num_intersects, xys, depths, radii, cum_t
     """utils.py:121-167; tile_bins gets max(num_intersects, TX*TY) rows (Q4 made safe)."""
     ids, gids = map_gaussian_to_intersects(num_points, num_intersects, xys, depths, radii, cum_tiles_hit, tile_bounds_)
     ids_s, gids_s = sort_intersects(ids, gids)
-    bins = get_tile_bin_edges(num_intersects, ids_s, max(num_intersects, tile_bounds_[0] * tile_bounds_[1]))
+    bins = get_tile_bin_edges(num_intersects, ids_s, max(int(num_intersects), int(tile_bounds_[0]) * int(tile_bounds_[1])))
     return ids, gids, ids_s, gids_s, bins
 
 
