@@ -151,51 +151,62 @@ class _RasterizeGaussiansSum(Function):
         return (v_xy, None, None, v_conic, None, v_colors, v_opacity, None, None, None, None, None, None)
 
 
+def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap, want_aux=False):
+    """One asynchronous pass of the fused chain (csrc/binning.cu gi2d_bin_fused + csrc/raster.cu packed forward) on the
+    current stream with an intersection capacity `cap`.  Returns a dict of device tensors:
+    out_img, final_Ts/final_idx (or None), tile_bins (T,2), packed (cap*12), gids_sorted (cap), status (2,) = [n, overflow]."""
+    dev = xys.device
+    L = lib()
+    N = xys.size(0)
+    TX, TY = (W + 15) // 16, (H + 15) // 16
+    stream = _C._stream(dev)
+    ws_bytes = L.gi2d_bin_fused_workspace_bytes(N, TX, TY, cap)
+    # one scratch allocation: [workspace | gids_sorted | status]; tile_bins and packed are kept for backward
+    o_gids = _align(ws_bytes)
+    o_status = o_gids + _align(4 * cap)
+    scratch = torch.empty((o_status + 256,), dtype=torch.uint8, device=dev)
+    tile_bins = torch.empty((TX * TY, 2), dtype=torch.int32, device=dev)
+    packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
+    base = scratch.data_ptr()
+    check(L.gi2d_bin_fused(N, TX, TY, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(), conics.data_ptr(),
+                           colors.data_ptr(), opacity.data_ptr(), cap, base, ws_bytes, base + o_gids,
+                           tile_bins.data_ptr(), packed.data_ptr(), base + o_status, stream), "bin_fused")
+    out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+    final_Ts = torch.empty((H, W), dtype=torch.float32, device=dev) if want_aux else None
+    final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if want_aux else None
+    check(L.gi2d_raster_sum_fwd_packed(TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(), base + o_status,
+                                       background.data_ptr(), out_img.data_ptr(), _C._p(final_Ts),
+                                       _C._p(final_idx), stream), "rasterize_sum_forward")
+    return dict(out_img=out_img, final_Ts=final_Ts, final_idx=final_idx, tile_bins=tile_bins, packed=packed,
+                gids_sorted=scratch[o_gids:o_gids + 4 * cap].view(torch.int32),
+                status=scratch[o_status:o_status + 8].view(torch.int32))
+
+
 def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background, want_aux):
     N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
     dev = xys.device
-    L = lib()
     xys, conics, colors = _C._f32(xys, "xys"), _C._f32(conics, "conics"), _C._f32(colors, "colors")
     opacity, background = _C._f32(opacity, "opacity"), _C._f32(background.to(dev), "background")
     radii, nth = _C._i32(radii, "radii"), _C._i32(num_tiles_hit, "num_tiles_hit")
     ctx.opacity_shape = opacity.shape
     key = (dev.index, N, TX, TY)
-    capturing = torch.cuda.is_current_stream_capturing()
-    strict = not (_sync_free or capturing)
+    strict = not (_sync_free or torch.cuda.is_current_stream_capturing())
     with torch.cuda.device(dev):
-        stream = _C._stream(dev)
         while True:
             cap = _capacity.get(key)
             if cap is None:
                 cap = _capacity[key] = max(4 * N, 1 << 14)
-            ws_bytes = L.gi2d_bin_fused_workspace_bytes(N, TX, TY, cap)
-            # one allocation: [workspace | gids_sorted | status]; tile_bins and packed are kept for backward
-            o_gids = _align(ws_bytes)
-            o_status = o_gids + _align(4 * cap)
-            scratch = torch.empty((o_status + 256,), dtype=torch.uint8, device=dev)
-            tile_bins = torch.empty((TX * TY, 2), dtype=torch.int32, device=dev)
-            packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
-            base = scratch.data_ptr()
-            check(L.gi2d_bin_fused(N, TX, TY, xys.data_ptr(), radii.data_ptr(), nth.data_ptr(), conics.data_ptr(),
-                                   colors.data_ptr(), opacity.data_ptr(), cap, base, ws_bytes, base + o_gids,
-                                   tile_bins.data_ptr(), packed.data_ptr(), base + o_status, stream), "bin_fused")
-            out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
-            final_Ts = torch.empty((H, W), dtype=torch.float32, device=dev) if want_aux else None
-            final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if want_aux else None
-            check(L.gi2d_raster_sum_fwd_packed(TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(), base + o_status,
-                                               background.data_ptr(), out_img.data_ptr(), _C._p(final_Ts),
-                                               _C._p(final_idx), stream), "rasterize_sum_forward")
-            status = scratch[o_status:o_status + 8].view(torch.int32)
-            _last_status[dev.index] = (status, cap, key)
+            r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux)
+            _last_status[dev.index] = (r["status"], cap, key)
             if not strict:
                 break
-            n, over = status.tolist()              # the single device->host read, after everything is enqueued
+            n, over = r["status"].tolist()         # the single device->host read, after everything is enqueued
             if not over:
                 ctx.num_intersects = n
                 break
             _capacity[key] = int(n * 1.25) + 1024  # truncated: grow and redo
-    ctx.save_for_backward(tile_bins, packed)
-    return out_img, final_Ts
+    ctx.save_for_backward(r["tile_bins"], r["packed"])
+    return r["out_img"], r["final_Ts"]
 
 
 def _forward_staged(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity, background):

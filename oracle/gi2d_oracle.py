@@ -215,3 +215,18 @@ def fit_step_cholesky(means2d, L, colors, opac, gt, H, W):
                                                        st["conics"], colors, opac, st["final_idx"], v_out)
     _, v_mean, v_L = project_gaussians_2d_backward(L, H, W, st["radii"], st["conics"], v_xy, v_conic)
     return loss, dict(v_means2d=v_mean, v_L=v_L, v_colors=v_col, v_opacity=v_op, v_xy=v_xy, v_conic=v_conic)
+
+
+def fit_step_scale_rot(means2d, scales, rot, colors, opac, gt, H, W):
+    """The same step for the scale-rotation model (gaussianimage_rs.py:74-95)."""
+    TX, TY = tile_bounds(H, W)
+    xys, depths, radii, conics, nth = project_gaussians_2d_scale_rot(means2d, scales, rot, H, W)
+    n, cum = compute_cumulative_intersects(nth)
+    ids, gids, ids_s, gids_s, bins = bin_and_sort_gaussians(means2d.shape[0], n, xys, depths, radii, cum, (TX, TY, 1))
+    out, Ts, fidx = rasterize_sum_forward(H, W, gids_s, bins, xys, conics, colors, opac)
+    diff = out - gt
+    loss = float(np.mean(diff.astype(np.float64) ** 2))
+    v_out = (2.0 / diff.size) * diff
+    v_xy, v_conic, v_col, v_op = rasterize_sum_backward(H, W, gids_s, bins, xys, conics, colors, opac, fidx, v_out)
+    _, v_mean, v_scale, v_rot = project_gaussians_2d_scale_rot_backward(scales, rot, H, W, radii, conics, v_xy, v_conic)
+    return loss, dict(v_means2d=v_mean, v_scale=v_scale, v_rot=v_rot, v_colors=v_col, v_opacity=v_op)

