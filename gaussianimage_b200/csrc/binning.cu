@@ -54,20 +54,21 @@ __device__ __forceinline__ int warp_sum(int v) {
     return v;
 }
 
-// Block-wide inclusive scan of one int per thread (SB threads). Returns the inclusive value; *block_total = sum.
-__device__ __forceinline__ int block_incl_scan(int v, int *s_warp /*SB/32*/, int *block_total) {
+// Block-wide inclusive scan of one int per thread (NT threads). Returns the inclusive value; *block_total = sum.
+template <int NT>
+__device__ __forceinline__ int block_incl_scan(int v, int *s_warp /*NT/32*/, int *block_total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int incl = warp_incl_scan(v, lane);
     if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
     if (warp == 0) {
-        int w = lane < SB / 32 ? s_warp[lane] : 0;
+        int w = lane < NT / 32 ? s_warp[lane] : 0;
         w = warp_incl_scan(w, lane);
-        if (lane < SB / 32) s_warp[lane] = w;
+        if (lane < NT / 32) s_warp[lane] = w;
     }
     __syncthreads();
     if (warp > 0) incl += s_warp[warp - 1];
-    *block_total = s_warp[SB / 32 - 1];
+    *block_total = s_warp[NT / 32 - 1];
     return incl;
 }
 
@@ -162,28 +163,31 @@ __device__ __forceinline__ void gaussian_bbox(const float *__restrict__ xys, con
 }
 
 // Inclusive int32 scan of num_tiles_hit (utils.py:116) -> cum (may be null) and the total in ctl[CTL_N].
-// FUSED additionally emits the compact (tile, gid) pairs and the digit histograms, and zeroes tile_bins.
+// FUSED additionally emits the compact (tile, gid) pairs and the digit histograms, presets tile_bins to
+// (INT_MAX, 0) for the atomicMin/Max of the last sort pass and writes status_out = {n_isect, overflow}.
+// One Gaussian per thread, SCAN_T threads per block: 70k Gaussians are 69 blocks, so the look-back chain is short.
+constexpr int SCAN_T = 1024;
 template <bool FUSED>
-__global__ void __launch_bounds__(SB) scan_kernel(int N, const int *__restrict__ num_tiles_hit, int *__restrict__ cum,
-                                                  uint32_t *ctl, uint32_t *scan_state, const float *__restrict__ xys,
-                                                  const int *__restrict__ radii, int TX, int TY, int capacity,
-                                                  uint32_t *keys_out, int *vals_out, PassPlan plan,
-                                                  int *tile_bins_zero, int tile_bins_words) {
-    __shared__ int s_warp[SB / 32];
+__global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restrict__ num_tiles_hit, int *__restrict__ cum,
+                                                      uint32_t *ctl, uint32_t *scan_state, const float *__restrict__ xys,
+                                                      const int *__restrict__ radii, int TX, int TY, int capacity,
+                                                      uint32_t *keys_out, int *vals_out, PassPlan plan,
+                                                      int2 *tile_bins_init, int n_bins, int *status_out, int use_ticket) {
+    __shared__ int s_warp[SCAN_T / 32];
     __shared__ int s_bcast[2];
     __shared__ uint32_t s_hist[FUSED ? MAX_PASSES * RADIX : 1];
     const int tid = threadIdx.x;
     if (FUSED) {
-        for (int k = blockIdx.x * SB + tid; k < tile_bins_words; k += gridDim.x * SB) tile_bins_zero[k] = 0;
-        for (int k = tid; k < plan.npass * RADIX; k += SB) s_hist[k] = 0;
+        for (int k = blockIdx.x * SCAN_T + tid; k < n_bins; k += gridDim.x * SCAN_T) tile_bins_init[k] = make_int2(0x7fffffff, 0);
+        for (int k = tid; k < plan.npass * RADIX; k += SCAN_T) s_hist[k] = 0;
     }
-    if (tid == 0) s_bcast[0] = (int)atomicAdd(ctl + CTL_SCAN_TICKET, 1u);   // virtual block id: look-back order = start order
+    if (use_ticket && tid == 0) s_bcast[0] = (int)atomicAdd(ctl + CTL_SCAN_TICKET, 1u);   // look-back order = start order
     __syncthreads();
-    const int vbid = s_bcast[0];
-    const int i = vbid * SB + tid;
+    const int vbid = use_ticket ? s_bcast[0] : (int)blockIdx.x;
+    const int i = vbid * SCAN_T + tid;
     const int cnt = i < N ? __ldg(num_tiles_hit + i) : 0;
     int block_total;
-    const int incl = block_incl_scan(cnt, s_warp, &block_total);
+    const int incl = block_incl_scan<SCAN_T>(cnt, s_warp, &block_total);
     if (tid < 32) {
         const int e = lookback_exclusive(scan_state, vbid, block_total);
         if (tid == 0) s_bcast[1] = e;
@@ -194,14 +198,18 @@ __global__ void __launch_bounds__(SB) scan_kernel(int N, const int *__restrict__
     if (vbid == (int)gridDim.x - 1 && tid == 0) {
         const int total = block_excl + block_total;
         ctl[CTL_N] = (uint32_t)total;
-        if (FUSED && total > capacity) ctl[CTL_OVERFLOW] = 1u;
+        if (FUSED) {
+            const int over = total > capacity ? 1 : 0;
+            ctl[CTL_OVERFLOW] = (uint32_t)over;
+            if (status_out) { status_out[0] = total; status_out[1] = over; }
+        }
     }
     if (FUSED) {
         int x0 = 0, w = 1, y0 = 0, area = 0;
         if (i < N && cnt > 0) gaussian_bbox(xys, radii, i, TX, TY, x0, w, y0, area);
         warp_emit<0>(cnt, block_excl + incl - cnt, x0, w, y0, area, i, 0, TX, capacity, keys_out, vals_out, s_hist, plan);
         __syncthreads();
-        for (int k = tid; k < plan.npass * RADIX; k += SB) {
+        for (int k = tid; k < plan.npass * RADIX; k += SCAN_T) {
             const uint32_t c = s_hist[k];
             if (c) atomicAdd(ctl + CTL_HIST + k, c);
         }
@@ -245,44 +253,76 @@ __global__ void __launch_bounds__(SB) hist_kernel(int n, const KeyT *__restrict_
     }
 }
 
-// One onesweep pass. Block tile = SB*ITEMS keys, warp-striped so that (item, lane) order == memory order.
-template <typename KeyT, int ITEMS>
+// Exclusive scan of one value per thread over the SB threads of the block (s_tmp: SB/32 words; contains barriers).
+__device__ __forceinline__ uint32_t block_excl_scan_u32(uint32_t v, uint32_t *s_tmp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t incl = (uint32_t)warp_incl_scan((int)v, lane);
+    __syncthreads();                       // s_tmp may still be read from a previous call
+    if (lane == 31) s_tmp[warp] = incl;
+    __syncthreads();
+    uint32_t wprefix = 0;
+#pragma unroll
+    for (int w = 0; w < SB / 32; ++w) wprefix += (w < warp) ? s_tmp[w] : 0;
+    return wprefix + incl - v;
+}
+
+struct PackSrc {          // sources of the packed records written by the LAST pass of the fused chain
+    const float *xys, *conics, *colors, *opac;
+    float4 *packed;
+    int *tile_bins;       // (n_bins,2), pre-set to (INT_MAX, 0) by the scan kernel
+    int n_bins;
+};
+
+// One onesweep pass.  Block tile = SB*ITEMS keys, warp-striped so that (item, lane) order == memory order.
+//   1. rank the keys of the tile by digit (warp match_any multisplit, stable);
+//   2. thread d owns digit d: block count, decoupled look-back over the preceding blocks (8 loads in flight per
+//      step), global digit base from the pass histogram;
+//   3. stage (key, value) in shared memory in block-sorted order, then write them out with consecutive threads on
+//      consecutive addresses of each digit run.
+// LAST (fused chain, uint32 tile keys, most significant digit): the sorted keys themselves are not written; instead
+// the per-tile bin edges are derived from neighbouring keys (atomicMin/Max only matter at block/digit seams) and the
+// 48-byte packed record of each intersection is gathered and written at its sorted position.
+template <typename KeyT, int ITEMS, bool LAST>
 __global__ void __launch_bounds__(SB) onesweep_kernel(const uint32_t *__restrict__ d_n, int n_host, int capacity,
                                                       const KeyT *__restrict__ keys_in, const int *__restrict__ vals_in,
                                                       KeyT *__restrict__ keys_out, int *__restrict__ vals_out,
                                                       uint32_t *ctl, uint32_t *lookback /* [blocks][RADIX] */, int pass,
-                                                      int shift, int bits, KeyT flip) {
+                                                      int shift, int bits, KeyT flip, int use_ticket, PackSrc ps) {
     constexpr int WARPS = SB / 32, TILE = SB * ITEMS;
     __shared__ uint32_t s_cnt[WARPS][RADIX];     // per-warp digit counts, then per-warp exclusive offsets
-    __shared__ uint32_t s_base[RADIX];           // global output position of this block's first key of each digit
-    __shared__ uint32_t s_scan[WARPS];
+    __shared__ uint32_t s_off[RADIX];            // block-exclusive offset of each digit's run in the staged order
+    __shared__ uint32_t s_base[RADIX];           // global position of staged index 0 of each digit's run, minus s_off
+    __shared__ uint32_t s_tmp[WARPS];
+    __shared__ KeyT s_keys[TILE];
+    __shared__ int s_vals[TILE];
     __shared__ int s_vbid;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = d_n ? min((int)*d_n, capacity) : n_host;
-    if (tid == 0) s_vbid = (int)atomicAdd(ctl + CTL_SORT_TICKET + pass, 1u);
+    if (use_ticket && tid == 0) s_vbid = (int)atomicAdd(ctl + CTL_SORT_TICKET + pass, 1u);
 #pragma unroll
     for (int w = 0; w < WARPS; ++w) s_cnt[w][tid] = 0;
     __syncthreads();
-    const int vbid = s_vbid;
+    const int vbid = use_ticket ? s_vbid : (int)blockIdx.x;
     const int tile_start = vbid * TILE;
     if (tile_start >= n) return;                 // whole block past the end: nobody looks back at it
+    const int nvalid = min(TILE, n - tile_start);
     const uint32_t mask = (1u << bits) - 1;
 
     KeyT key[ITEMS];
     int val[ITEMS];
     uint32_t rank[ITEMS];
-    const int wbase = tile_start + warp * 32 * ITEMS + lane;
+    const int wofs = warp * 32 * ITEMS + lane;   // index inside the tile of this thread's item 0
 #pragma unroll
     for (int it = 0; it < ITEMS; ++it) {
-        const int idx = wbase + it * 32;
-        const bool ok = idx < n;
-        key[it] = ok ? keys_in[idx] : (KeyT)0;
-        val[it] = ok ? vals_in[idx] : 0;
+        const int li = wofs + it * 32;
+        const bool ok = li < nvalid;
+        key[it] = ok ? keys_in[tile_start + li] : (KeyT)0;
+        val[it] = ok ? vals_in[tile_start + li] : 0;
     }
     const unsigned lt_mask = (1u << lane) - 1;
 #pragma unroll
     for (int it = 0; it < ITEMS; ++it) {
-        const bool ok = wbase + it * 32 < n;
+        const bool ok = wofs + it * 32 < nvalid;
         const uint32_t digit = ok ? (uint32_t)(((key[it] ^ flip) >> shift) & (KeyT)mask) : RADIX;   // RADIX = "no key"
         const unsigned peers = __match_any_sync(0xffffffffu, digit);
         const uint32_t before = ok ? s_cnt[warp][digit] : 0;
@@ -292,8 +332,7 @@ __global__ void __launch_bounds__(SB) onesweep_kernel(const uint32_t *__restrict
         rank[it] = before + __popc(peers & lt_mask);
     }
     __syncthreads();
-    // thread d owns digit d: exclusive scan over warps, publish the block count, look back, add the global digit base
-    {
+    {   // thread d owns digit d
         uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < WARPS; ++w) {
@@ -303,33 +342,65 @@ __global__ void __launch_bounds__(SB) onesweep_kernel(const uint32_t *__restrict
         }
         uint32_t *my = lookback + (size_t)vbid * RADIX + tid;
         st_volatile(my, (vbid == 0 ? FLAG_INCL : FLAG_AGG) | run);
+        const uint32_t h = ctl[CTL_HIST + pass * RADIX + tid];
+        const uint32_t off = block_excl_scan_u32(run, s_tmp);      // run of digit d starts here in the staged order
+        const uint32_t gbase = block_excl_scan_u32(h, s_tmp);      // exclusive scan of the pass histogram
         uint32_t excl = 0;
-        for (int pb = vbid - 1; pb >= 0; --pb) {
-            const uint32_t *p = lookback + (size_t)pb * RADIX + tid;
-            uint32_t w;
-            do { w = ld_volatile(p); } while ((w >> 30) == 0);
-            excl += w & VAL_MASK;
-            if (w & FLAG_INCL) break;
+        int pb = vbid - 1;
+        while (pb >= 0) {
+            uint32_t w[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w[j] = (pb - j >= 0) ? ld_volatile(lookback + (size_t)(pb - j) * RADIX + tid) : FLAG_INCL;
+            int j = 0;
+            bool done = false;
+#pragma unroll
+            for (; j < 8; ++j) {
+                if ((w[j] >> 30) == 0) break;      // not published yet: re-read from here
+                excl += w[j] & VAL_MASK;
+                if (w[j] & FLAG_INCL) { done = true; break; }
+            }
+            if (done) break;
+            pb -= j;
         }
         if (vbid > 0) st_volatile(my, FLAG_INCL | (excl + run));
-        // exclusive scan of the global digit histogram of this pass (every block recomputes it: 256 adds)
-        const uint32_t h = ctl[CTL_HIST + pass * RADIX + tid];
-        uint32_t incl = (uint32_t)warp_incl_scan((int)h, lane);
-        if (lane == 31) s_scan[warp] = incl;
-        __syncthreads();
-        uint32_t wprefix = 0;
-#pragma unroll
-        for (int w = 0; w < WARPS; ++w) wprefix += (w < warp) ? s_scan[w] : 0;
-        s_base[tid] = wprefix + incl - h + excl;
+        s_off[tid] = off;
+        s_base[tid] = gbase + excl - off;
     }
     __syncthreads();
 #pragma unroll
     for (int it = 0; it < ITEMS; ++it) {
-        if (wbase + it * 32 < n) {
+        if (wofs + it * 32 < nvalid) {
             const uint32_t digit = (uint32_t)(((key[it] ^ flip) >> shift) & (KeyT)mask);
-            const uint32_t pos = s_base[digit] + s_cnt[warp][digit] + rank[it];
-            keys_out[pos] = key[it];
-            vals_out[pos] = val[it];
+            const uint32_t li = s_off[digit] + s_cnt[warp][digit] + rank[it];
+            s_keys[li] = key[it];
+            s_vals[li] = val[it];
+        }
+    }
+    __syncthreads();
+    for (int li = tid; li < nvalid; li += SB) {
+        const KeyT k = s_keys[li];
+        const int v = s_vals[li];
+        const uint32_t digit = (uint32_t)(((k ^ flip) >> shift) & (KeyT)mask);
+        const uint32_t pos = s_base[digit] + li;
+        vals_out[pos] = v;
+        if (!LAST) {
+            keys_out[pos] = k;
+        } else {
+            const int cur = (int)k;
+            if (cur < ps.n_bins) {
+                const bool first = li == 0 || (uint32_t)(((s_keys[li - 1] ^ flip) >> shift) & (KeyT)mask) != digit;
+                const bool last = li == nvalid - 1 || (uint32_t)(((s_keys[li + 1] ^ flip) >> shift) & (KeyT)mask) != digit;
+                if (first || (int)s_keys[li - 1] != cur) atomicMin(ps.tile_bins + 2 * cur, (int)pos);
+                if (last || (int)s_keys[li + 1] != cur) atomicMax(ps.tile_bins + 2 * cur + 1, (int)pos + 1);
+            }
+            const size_t g = (size_t)v;
+            const float x = __ldg(ps.xys + 2 * g), y = __ldg(ps.xys + 2 * g + 1);
+            const float cx = __ldg(ps.conics + 3 * g), cy = __ldg(ps.conics + 3 * g + 1), cz = __ldg(ps.conics + 3 * g + 2);
+            const float r = __ldg(ps.colors + 3 * g), gg = __ldg(ps.colors + 3 * g + 1), b = __ldg(ps.colors + 3 * g + 2);
+            const float o = __ldg(ps.opac + g);
+            ps.packed[3 * (size_t)pos + 0] = make_float4(x, y, o, cx);
+            ps.packed[3 * (size_t)pos + 1] = make_float4(cy, cz, r, gg);
+            ps.packed[3 * (size_t)pos + 2] = make_float4(b, __int_as_float(v), 0.f, 0.f);
         }
     }
 }
@@ -348,39 +419,6 @@ __global__ void __launch_bounds__(SB) tile_bins_kernel(int n, const KeyT *__rest
             if (prev >= 0 && prev < n_bins) tile_bins[2 * prev + 1] = i;
             if (cur_ok) tile_bins[2 * cur] = i;
         }
-    }
-}
-
-// Fused tail of the sync-free chain: tile bin edges + the packed per-intersection records
-//   rec[i] = { x, y, opacity, conic.x | conic.y, conic.z, r, g | b, gid, 0, 0 }   (3 x float4, 48 B)
-// gathered from the (N,*) tensors in sorted order, so that a tile's batch is one contiguous span for bulk TMA.
-__global__ void __launch_bounds__(SB) bins_pack_kernel(const uint32_t *__restrict__ ctl, int capacity,
-                                                       const uint32_t *__restrict__ keys_sorted,
-                                                       const int *__restrict__ gids_sorted, int n_bins, int *tile_bins,
-                                                       const float *__restrict__ xys, const float *__restrict__ conics,
-                                                       const float *__restrict__ colors, const float *__restrict__ opac,
-                                                       float4 *__restrict__ packed) {
-    const int n = min((int)ctl[CTL_N], capacity);
-    for (int i = blockIdx.x * SB + threadIdx.x; i < n; i += gridDim.x * SB) {
-        const int cur = (int)keys_sorted[i];
-        const bool cur_ok = cur < n_bins;
-        if (i == 0 && cur_ok) tile_bins[2 * cur] = 0;
-        if (i == n - 1 && cur_ok) tile_bins[2 * cur + 1] = n;
-        if (i > 0) {
-            const int prev = (int)keys_sorted[i - 1];
-            if (prev != cur) {
-                if (prev < n_bins) tile_bins[2 * prev + 1] = i;
-                if (cur_ok) tile_bins[2 * cur] = i;
-            }
-        }
-        const int g = gids_sorted[i];
-        const float x = __ldg(xys + 2 * (size_t)g), y = __ldg(xys + 2 * (size_t)g + 1);
-        const float cx = __ldg(conics + 3 * (size_t)g), cy = __ldg(conics + 3 * (size_t)g + 1), cz = __ldg(conics + 3 * (size_t)g + 2);
-        const float r = __ldg(colors + 3 * (size_t)g), gg = __ldg(colors + 3 * (size_t)g + 1), b = __ldg(colors + 3 * (size_t)g + 2);
-        const float o = __ldg(opac + g);
-        packed[3 * (size_t)i + 0] = make_float4(x, y, o, cx);
-        packed[3 * (size_t)i + 1] = make_float4(cy, cz, r, gg);
-        packed[3 * (size_t)i + 2] = make_float4(b, __int_as_float(g), 0.f, 0.f);
     }
 }
 
@@ -403,8 +441,22 @@ static PassPlan make_plan(int lo_bit, int hi_bit) {   // sort key bits [lo_bit, 
     return p;
 }
 
-constexpr int SORT_ITEMS = 4;
-constexpr int SORT_TILE = SB * SORT_ITEMS;
+constexpr int SORT_ITEMS32 = 16, SORT_TILE32 = SB * SORT_ITEMS32;   // uint32 keys: 4096 per block (41 KB shared)
+constexpr int SORT_ITEMS64 = 8, SORT_TILE64 = SB * SORT_ITEMS64;    // int64 keys: 2048 per block (33 KB shared)
+
+// Look-back order may be blockIdx order when every block of the grid is resident at once (no ticket atomics).
+template <typename K>
+static bool all_resident(K kernel, int threads, int grid) {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess) return false;
+    return grid <= per_sm * sms;
+}
 
 struct FusedLayout {          // carve-up of the caller's workspace for gi2d_bin_fused
     size_t ctl, scan_state, lookback, zero_bytes, keys_a, keys_b, vals_b, total;
@@ -413,8 +465,8 @@ struct FusedLayout {          // carve-up of the caller's workspace for gi2d_bin
 static FusedLayout fused_layout(int N, int T, int capacity) {
     FusedLayout L;
     L.npass = make_plan(0, ceil_log2(T > 1 ? T : 2)).npass;
-    L.scan_blocks = (N + SB - 1) / SB;
-    L.sort_blocks = (capacity + SORT_TILE - 1) / SORT_TILE;
+    L.scan_blocks = (N + SCAN_T - 1) / SCAN_T;
+    L.sort_blocks = (capacity + SORT_TILE32 - 1) / SORT_TILE32;
     size_t o = 0;
     L.ctl = o; o += align_up(sizeof(uint32_t) * CTL_WORDS, 256);
     L.scan_state = o; o += align_up(sizeof(uint32_t) * (size_t)L.scan_blocks, 256);
@@ -436,7 +488,7 @@ extern "C" {
 // ---- staged, reference-typed entry points ------------------------------------------------------------------------
 
 size_t gi2d_scan_workspace_bytes(int N) {
-    return align_up(sizeof(uint32_t) * CTL_WORDS, 256) + align_up(sizeof(uint32_t) * (size_t)((N + SB - 1) / SB), 256);
+    return align_up(sizeof(uint32_t) * CTL_WORDS, 256) + align_up(sizeof(uint32_t) * (size_t)((N + SCAN_T - 1) / SCAN_T), 256);
 }
 
 // compute_cumulative_intersects (utils.py:99-118): cum (N,) int32 inclusive; the total is written to *total_out
@@ -451,8 +503,10 @@ int gi2d_scan_tiles(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *to
     cudaMemsetAsync(ws, 0, need, stream);
     PassPlan none;
     none.npass = 0;
-    scan_kernel<false><<<(N + SB - 1) / SB, SB, 0, stream>>>(N, num_tiles_hit, cum_tiles_hit, ctl, state, nullptr, nullptr, 0, 0, 0,
-                                                          nullptr, nullptr, none, nullptr, 0);
+    const int grid = (N + SCAN_T - 1) / SCAN_T;
+    const int ticket = all_resident(scan_kernel<false>, SCAN_T, grid) ? 0 : 1;
+    scan_kernel<false><<<grid, SCAN_T, 0, stream>>>(N, num_tiles_hit, cum_tiles_hit, ctl, state, nullptr, nullptr, 0, 0, 0, nullptr,
+                                                   nullptr, none, nullptr, 0, nullptr, ticket);
     if (total_out) cudaMemcpyAsync(total_out, ctl + CTL_N, sizeof(int), cudaMemcpyDefault, stream);
     return cuda_status();
 }
@@ -471,7 +525,7 @@ int gi2d_emit_isects(int N, const float *xys, const float *depths, const int *ra
 
 size_t gi2d_sort_workspace_bytes(int n, int begin_bit, int end_bit) {
     const PassPlan plan = make_plan(begin_bit, end_bit);
-    const int blocks = (n + SORT_TILE - 1) / SORT_TILE;
+    const int blocks = (n + SORT_TILE64 - 1) / SORT_TILE64;
     size_t o = align_up(sizeof(uint32_t) * CTL_WORDS, 256);
     o += align_up(sizeof(uint32_t) * (size_t)plan.npass * blocks * RADIX, 256);
     o += align_up(sizeof(long long) * (size_t)n, 256) + align_up(sizeof(int) * (size_t)n, 256);
@@ -486,7 +540,7 @@ int gi2d_sort_isects(int n, const long long *ids_in, const int *gids_in, long lo
     if (n == 0) return GI2D_OK;
     if (ws_bytes < gi2d_sort_workspace_bytes(n, begin_bit, end_bit)) return GI2D_ERR_WORKSPACE;
     const PassPlan plan = make_plan(begin_bit, end_bit);
-    const int blocks = (n + SORT_TILE - 1) / SORT_TILE;
+    const int blocks = (n + SORT_TILE64 - 1) / SORT_TILE64;
     char *base = reinterpret_cast<char *>(ws);
     size_t o = 0;
     uint32_t *ctl = reinterpret_cast<uint32_t *>(base + o); o += align_up(sizeof(uint32_t) * CTL_WORDS, 256);
@@ -499,6 +553,8 @@ int gi2d_sort_isects(int n, const long long *ids_in, const int *gids_in, long lo
     const unsigned long long *kin = reinterpret_cast<const unsigned long long *>(ids_in);
     unsigned long long *kout = reinterpret_cast<unsigned long long *>(ids_out);
     hist_kernel<unsigned long long><<<min(blocks, 1024), SB, 0, stream>>>(n, kin, ctl, plan, flip);
+    const int ticket = all_resident(onesweep_kernel<unsigned long long, SORT_ITEMS64, false>, SB, blocks) ? 0 : 1;
+    PackSrc none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
     // ping-pong so that the last pass lands in (ids_out, gids_out)
     const unsigned long long *src_k = kin;
     const int *src_v = gids_in;
@@ -506,8 +562,9 @@ int gi2d_sort_isects(int n, const long long *ids_in, const int *gids_in, long lo
         const bool to_out = ((plan.npass - 1 - p) % 2) == 0;
         unsigned long long *dst_k = to_out ? kout : tmp_k;
         int *dst_v = to_out ? gids_out : tmp_v;
-        onesweep_kernel<unsigned long long, SORT_ITEMS><<<blocks, SB, 0, stream>>>(
-            nullptr, n, n, src_k, src_v, dst_k, dst_v, ctl, lookback + (size_t)p * blocks * RADIX, p, plan.shift[p], plan.bits[p], flip);
+        onesweep_kernel<unsigned long long, SORT_ITEMS64, false><<<blocks, SB, 0, stream>>>(
+            nullptr, n, n, src_k, src_v, dst_k, dst_v, ctl, lookback + (size_t)p * blocks * RADIX, p, plan.shift[p], plan.bits[p], flip,
+            ticket, none);
         src_k = dst_k;
         src_v = dst_v;
     }
@@ -530,9 +587,12 @@ size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity) {
     return fused_layout(N, TX * TY, capacity).total;
 }
 
-// scan + emit + sort + bin edges + record packing with the intersection count left on the device.
+// scan + emit + sort + bin edges + record packing with the intersection count left on the device:
+//   memset(control) -> scan_kernel<FUSED> -> onesweep pass(es) -> last onesweep pass (+ bin edges + packed records)
 //   status_out[0] = n_isect (may exceed capacity), status_out[1] = 1 when n_isect > capacity (results truncated).
-//   gids_sorted (capacity,) int32, tile_bins (TX*TY,2) int32, packed (capacity*3) float4.
+//   gids_sorted (capacity,) int32, packed (capacity*3) float4,
+//   tile_bins (TX*TY,2) int32: [lo,hi) per tile; EMPTY tiles hold (INT_MAX, 0) until gi2d_raster_sum_fwd_packed
+//   rewrites them to the reference's (0, 0).
 // Precondition (2D path): depths are all zero, so the key is the tile id alone.
 int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, const int *num_tiles_hit,
                    const float *conics, const float *colors, const float *opacities, int capacity, void *ws,
@@ -555,23 +615,27 @@ int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, co
     // values ping-pong between gids_sorted and vals_b; start so that the last pass lands in gids_sorted
     int *v0 = (plan.npass % 2 == 0) ? gids_sorted : vals_b;
     uint32_t *k0 = keys_a;
-    scan_kernel<true><<<L.scan_blocks, SB, 0, stream>>>(N, num_tiles_hit, nullptr, ctl, scan_state, xys, radii, TX, TY, capacity, k0,
-                                                       v0, plan, tile_bins, 2 * T);
+    const int scan_ticket = all_resident(scan_kernel<true>, SCAN_T, L.scan_blocks) ? 0 : 1;
+    scan_kernel<true><<<L.scan_blocks, SCAN_T, 0, stream>>>(N, num_tiles_hit, nullptr, ctl, scan_state, xys, radii, TX, TY, capacity, k0,
+                                                           v0, plan, reinterpret_cast<int2 *>(tile_bins), T, status_out, scan_ticket);
+    const int sort_ticket = all_resident(onesweep_kernel<uint32_t, SORT_ITEMS32, true>, SB, L.sort_blocks) ? 0 : 1;
+    PackSrc none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
+    PackSrc ps{xys, conics, colors, opacities, reinterpret_cast<float4 *>(packed), tile_bins, T};
     const uint32_t *src_k = k0;
     const int *src_v = v0;
     for (int p = 0; p < plan.npass; ++p) {
         uint32_t *dst_k = (src_k == keys_a) ? keys_b : keys_a;
         int *dst_v = (src_v == gids_sorted) ? vals_b : gids_sorted;
-        onesweep_kernel<uint32_t, SORT_ITEMS><<<L.sort_blocks, SB, 0, stream>>>(
-            ctl + CTL_N, 0, capacity, src_k, src_v, dst_k, dst_v, ctl, lookback + (size_t)p * L.sort_blocks * RADIX, p,
-            plan.shift[p], plan.bits[p], 0u);
+        uint32_t *lb = lookback + (size_t)p * L.sort_blocks * RADIX;
+        if (p == plan.npass - 1)
+            onesweep_kernel<uint32_t, SORT_ITEMS32, true><<<L.sort_blocks, SB, 0, stream>>>(
+                ctl + CTL_N, 0, capacity, src_k, src_v, dst_k, dst_v, ctl, lb, p, plan.shift[p], plan.bits[p], 0u, sort_ticket, ps);
+        else
+            onesweep_kernel<uint32_t, SORT_ITEMS32, false><<<L.sort_blocks, SB, 0, stream>>>(
+                ctl + CTL_N, 0, capacity, src_k, src_v, dst_k, dst_v, ctl, lb, p, plan.shift[p], plan.bits[p], 0u, sort_ticket, none);
         src_k = dst_k;
         src_v = dst_v;
     }
-    const int pack_blocks = min((capacity + SB - 1) / SB, 148 * 8);
-    bins_pack_kernel<<<pack_blocks, SB, 0, stream>>>(ctl, capacity, src_k, gids_sorted, T, tile_bins, xys, conics, colors, opacities,
-                                                     reinterpret_cast<float4 *>(packed));
-    if (status_out) cudaMemcpyAsync(status_out, ctl, 2 * sizeof(int), cudaMemcpyDeviceToDevice, stream);
     return cuda_status();
 }
 

@@ -11,9 +11,10 @@
 //     removes pairs the reference rejects, so no output bit changes;
 //   * forward: pixel-parallel, a warp owns an 8x4 pixel block and walks only the records whose extent touches
 //     that block (per-warp compacted index list);
-//   * backward: Gaussian-parallel -- one thread per staged record loops over the pixels of its extent, keeps
-//     the 9 partial gradients in registers and issues one set of 9 atomic adds per (tile, Gaussian); no shuffle
-//     reductions.  (The sum rasterizer has no transmittance chain, so the order over pixels is free.)
+//   * backward: row-parallel over the records' visible rectangles -- a thread owns one pixel row of one record,
+//     keeps the 9 partial gradients in registers, combines rows in shared memory and issues one set of 9 atomic
+//     adds per (tile, Gaussian); no shuffle reductions.  (The sum rasterizer has no transmittance chain, so the
+//     order over pixels is free.)
 // Per-pair arithmetic up to the two comparisons is the reference's instruction sequence (gi2d_common.cuh).
 // FP32-pipe bound; no tensor cores (not a dense contraction).
 #include "gi2d_common.cuh"
@@ -77,7 +78,7 @@ __device__ __forceinline__ bool record_rect(const float4 &A, const float4 &B, in
 }
 
 template <bool TMA, bool AUX>
-__global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, const int *__restrict__ tile_bins,
+__global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, int *tile_bins,
                                                         const float4 *__restrict__ packed, GatherSrc src,
                                                         const int *__restrict__ d_status,
                                                         const float *__restrict__ background, float *__restrict__ out_img,
@@ -97,9 +98,11 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, co
     const bool inside = i < H && j < W;
     const size_t pix = (size_t)i * W + j;
 
-    const int2 range = __ldg(reinterpret_cast<const int2 *>(tile_bins) + tile);
+    const int2 range = reinterpret_cast<const int2 *>(tile_bins)[tile];
     const int lo = range.x;
     const int cnt = min(range.y - range.x, GI2D_BATCH);          // Q1: only the first 256 sorted intersections count
+    if (TMA && tid == 0 && range.x == 0x7fffffff)                // empty tile left at (INT_MAX, 0) by gi2d_bin_fused:
+        reinterpret_cast<int2 *>(tile_bins)[tile] = make_int2(0, 0);   // canonical (0, 0) like the reference's zero fill
 
     float r = 0.f, g = 0.f, b = 0.f, T_final = 1.f;   // T is never updated in the sum rasterizer (Q6)
     int cur = 0;
@@ -155,6 +158,11 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, co
     }
 }
 
+// Backward.  Work item = one pixel ROW of one staged record's visible rectangle ("row-parallel"): the 256 threads
+// of the CTA walk the flattened list of rows of all records of the tile, so lanes stay busy regardless of how the
+// records' footprints differ; a thread accumulates its row's 9 partial gradients in registers, adds them to the
+// CTA's shared accumulators (one slot set per record) and at the end each record issues ONE set of 9 global atomic
+// adds per tile.  No warp-shuffle reductions, no per-pixel atomics.
 template <bool TMA>
 __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, const int *__restrict__ tile_bins,
                                                         const float4 *__restrict__ packed, GatherSrc src,
@@ -163,9 +171,14 @@ __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, co
                                                         float *__restrict__ v_opacity) {
     __shared__ __align__(128) float4 s_rec[RB * 3];
     __shared__ __align__(16) float4 s_vout[GI2D_TILE_PIX];
+    __shared__ float s_acc[9][RB];                   // [component][record]: conflict-free for per-record access
+    __shared__ uint32_t s_rect[RB];                  // lx0 | lx1<<8 | ly0<<16 | rows<<24
+    __shared__ uint16_t s_pref[RB];                  // exclusive prefix of the row counts
+    __shared__ uint8_t s_owner[RB * GI2D_TILE];      // flattened row index -> record
+    __shared__ int s_warp[RB / 32];
     __shared__ __align__(8) uint64_t s_bar;
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
     const int ty = tile / TX, tx = tile - ty * TX;
     const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
@@ -183,47 +196,88 @@ __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, co
             v.x = __ldg(v_out + 3 * pix); v.y = __ldg(v_out + 3 * pix + 1); v.z = __ldg(v_out + 3 * pix + 2);
         }
         s_vout[tid] = v;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) s_acc[k][tid] = 0.f;
     }
-    stage_records<TMA>(s_rec, &s_bar, packed, src, lo, cnt);   // ends with a CTA-wide barrier / mbarrier wait
-    __syncthreads();
-    if (tid >= cnt) return;
+    stage_records<TMA>(s_rec, &s_bar, packed, src, lo, cnt);
 
-    const float4 A = s_rec[3 * tid], B = s_rec[3 * tid + 1];
-    const float4 C = s_rec[3 * tid + 2];
-    int lx0, lx1, ly0, ly1;
-    if (!record_rect(A, B, tx0, ty0, lx0, lx1, ly0, ly1)) return;
-    const float x = A.x, y = A.y, opac = A.z, cx = A.w, cy = B.x, cz = B.y;
-    const float cr = B.z, cg = B.w, cb = C.x;
-    float a_r = 0.f, a_g = 0.f, a_b = 0.f, a_cxx = 0.f, a_cxy = 0.f, a_cyy = 0.f, a_x = 0.f, a_y = 0.f, a_o = 0.f;
-    bool any = false;
-    for (int ly = ly0; ly <= ly1; ++ly) {
-        const float dy = fsub(y, (float)(ty0 + ly));
+    // per record: visible rectangle and its row count; block-wide exclusive scan of the row counts
+    int rows = 0, lx0 = 0, lx1 = 0, ly0 = 0, ly1 = 0;
+    if (tid < cnt && record_rect(s_rec[3 * tid], s_rec[3 * tid + 1], tx0, ty0, lx0, lx1, ly0, ly1)) rows = ly1 - ly0 + 1;
+    s_rect[tid] = (uint32_t)lx0 | ((uint32_t)lx1 << 8) | ((uint32_t)ly0 << 16) | ((uint32_t)rows << 24);
+    int incl = rows;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int wbase = 0;
+#pragma unroll
+    for (int w = 0; w < RB / 32; ++w) wbase += (w < warp) ? s_warp[w] : 0;
+    int total = 0;
+#pragma unroll
+    for (int w = 0; w < RB / 32; ++w) total += s_warp[w];
+    const int excl = wbase + incl - rows;
+    s_pref[tid] = (uint16_t)excl;
+    for (int q = 0; q < rows; ++q) s_owner[excl + q] = (uint8_t)tid;
+    __syncthreads();
+
+    for (int r = tid; r < total; r += RB) {
+        const int t = s_owner[r];
+        const uint32_t rect = s_rect[t];
+        const int x0 = rect & 0xff, x1 = (rect >> 8) & 0xff;
+        const int ly = (int)((rect >> 16) & 0xff) + (r - (int)s_pref[t]);
+        const float4 A = s_rec[3 * t], B = s_rec[3 * t + 1];
+        const float cb = s_rec[3 * t + 2].x;
+        const float x = A.x, opac = A.z, cx = A.w, cy = B.x, cz = B.y, cr = B.z, cg = B.w;
+        const float dy = fsub(A.y, (float)(ty0 + ly));
         const float t3 = fmul(dy, fmul(cz, dy));
-        for (int lx = lx0; lx <= lx1; ++lx) {
-            const float dx = fsub(x, (float)(tx0 + lx));
+        const float cydy = cy * dy, czdy = cz * dy;
+        float a_r = 0.f, a_g = 0.f, a_b = 0.f, a_cxx = 0.f, a_cxy = 0.f, a_cyy = 0.f, a_x = 0.f, a_y = 0.f, a_o = 0.f;
+        float fx = (float)(tx0 + x0);
+        const float4 *vrow = s_vout + ly * GI2D_TILE;
+        for (int lx = x0; lx <= x1; ++lx, fx += 1.f) {
+            const float dx = fsub(x, fx);
             const float q = ffma(dx, fmul(cx, dx), t3);
             const float sigma = ffma(dy, fmul(cy, dx), fmul(q, 0.5f));
-            const float vis = exp_neg(sigma);
-            const float alpha = fminf(fmul(opac, vis), 1.f);
-            if (sigma < 0.f || alpha < GI2D_ALPHA_MIN) continue;          // backward.cu:806-808
-            const float4 vo = s_vout[ly * GI2D_TILE + lx];
-            any = true;
-            a_r += alpha * vo.x; a_g += alpha * vo.y; a_b += alpha * vo.z;        // backward.cu:814
-            const float v_alpha = cr * vo.x + cg * vo.y + cb * vo.z;              // :818-820
-            const float v_sigma = -opac * vis * v_alpha;                          // :822
+            float vis = exp_neg(sigma);
+            const float raw = fmul(opac, vis);
+            const bool valid = !(sigma < 0.f) && !(fminf(raw, 1.f) < GI2D_ALPHA_MIN);     // backward.cu:806-808
+            const float alpha = valid ? fminf(raw, 1.f) : 0.f;
+            vis = valid ? vis : 0.f;
+            const float4 vo = vrow[lx];
+            a_r = fmaf(alpha, vo.x, a_r); a_g = fmaf(alpha, vo.y, a_g); a_b = fmaf(alpha, vo.z, a_b);   // backward.cu:814
+            const float v_alpha = fmaf(cr, vo.x, fmaf(cg, vo.y, cb * vo.z));                          // :818-820
+            const float v_sigma = -(opac * vis) * v_alpha;                                            // :822
             const float hs = 0.5f * v_sigma;
-            a_cxx += hs * dx * dx; a_cxy += hs * dx * dy; a_cyy += hs * dy * dy;  // :823-825
-            a_x += v_sigma * (cx * dx + cy * dy);                                 // :826-827
-            a_y += v_sigma * (cy * dx + cz * dy);
-            a_o += vis * v_alpha;                                                 // :828
+            const float hdx = hs * dx;
+            a_cxx = fmaf(hdx, dx, a_cxx); a_cxy = fmaf(hdx, dy, a_cxy); a_cyy = fmaf(hs * dy, dy, a_cyy);   // :823-825
+            a_x = fmaf(v_sigma, fmaf(cx, dx, cydy), a_x);                                             // :826-827
+            a_y = fmaf(v_sigma, fmaf(cy, dx, czdy), a_y);
+            a_o = fmaf(vis, v_alpha, a_o);                                                            // :828
+        }
+        if (a_r != 0.f || a_g != 0.f || a_b != 0.f || a_o != 0.f || a_x != 0.f || a_y != 0.f || a_cxx != 0.f || a_cxy != 0.f ||
+            a_cyy != 0.f) {
+            atomicAdd(&s_acc[0][t], a_x); atomicAdd(&s_acc[1][t], a_y);
+            atomicAdd(&s_acc[2][t], a_cxx); atomicAdd(&s_acc[3][t], a_cxy); atomicAdd(&s_acc[4][t], a_cyy);
+            atomicAdd(&s_acc[5][t], a_r); atomicAdd(&s_acc[6][t], a_g); atomicAdd(&s_acc[7][t], a_b);
+            atomicAdd(&s_acc[8][t], a_o);
         }
     }
+    __syncthreads();
+    if (tid >= cnt || rows == 0) return;
+    float g[9];
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { g[k] = s_acc[k][tid]; any |= g[k] != 0.f; }
     if (!any) return;
-    const int gid = __float_as_int(C.y);
-    atomicAdd(v_colors + 3 * (size_t)gid, a_r); atomicAdd(v_colors + 3 * (size_t)gid + 1, a_g); atomicAdd(v_colors + 3 * (size_t)gid + 2, a_b);
-    atomicAdd(v_conic + 3 * (size_t)gid, a_cxx); atomicAdd(v_conic + 3 * (size_t)gid + 1, a_cxy); atomicAdd(v_conic + 3 * (size_t)gid + 2, a_cyy);
-    atomicAdd(v_xy + 2 * (size_t)gid, a_x); atomicAdd(v_xy + 2 * (size_t)gid + 1, a_y);
-    atomicAdd(v_opacity + gid, a_o);
+    const int gid = __float_as_int(s_rec[3 * tid + 2].y);
+    atomicAdd(v_xy + 2 * (size_t)gid, g[0]); atomicAdd(v_xy + 2 * (size_t)gid + 1, g[1]);
+    atomicAdd(v_conic + 3 * (size_t)gid, g[2]); atomicAdd(v_conic + 3 * (size_t)gid + 1, g[3]); atomicAdd(v_conic + 3 * (size_t)gid + 2, g[4]);
+    atomicAdd(v_colors + 3 * (size_t)gid, g[5]); atomicAdd(v_colors + 3 * (size_t)gid + 1, g[6]); atomicAdd(v_colors + 3 * (size_t)gid + 2, g[7]);
+    atomicAdd(v_opacity + gid, g[8]);
 }
 
 static inline int cuda_status() {
@@ -245,15 +299,15 @@ int gi2d_raster_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, co
     if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0) return GI2D_ERR_INVALID;
     GatherSrc src{gids_sorted, xys, conics, colors, opacities};
     if (final_Ts && final_idx)
-        raster_fwd_kernel<false, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx);
+        raster_fwd_kernel<false, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx);
     else
-        raster_fwd_kernel<false, false><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, nullptr, src, nullptr, nullptr, out_img, nullptr, nullptr);
+        raster_fwd_kernel<false, false><<<TX * TY, RB, 0, stream>>>(TX, W, H, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, nullptr, nullptr);
     return cuda_status();
 }
 
 // Forward over the packed records of gi2d_bin_fused (bulk-TMA staging).  d_status[0] == 0 (no intersections
 // anywhere) makes the kernel write `background` instead, as rasterize_sum.py:121-129 does.
-int gi2d_raster_sum_fwd_packed(int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
+int gi2d_raster_sum_fwd_packed(int TX, int TY, int W, int H, int *tile_bins, const float *packed,
                                const int *d_status, const float *background, float *out_img, float *final_Ts,
                                int *final_idx, cudaStream_t stream) {
     if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0) return GI2D_ERR_INVALID;

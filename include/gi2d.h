@@ -100,7 +100,9 @@ int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *ti
 
 /* cumsum + map + sort + bin edges (utils.py:116-167) in one asynchronous chain with NO device->host read (the
  * reference's `.item()`, Q12): the intersection count stays on the device, `capacity` bounds it.
- *   gids_sorted (capacity) int32, tile_bins (TX*TY,2) int32,
+ *   gids_sorted (capacity) int32,
+ *   tile_bins (TX*TY,2) int32: [lo,hi) per tile; empty tiles hold (INT_MAX, 0) until gi2d_raster_sum_fwd_packed
+ *     rewrites them to the reference's (0, 0) -- consumers must treat lo >= hi as empty,
  *   packed (capacity*12 floats): per sorted intersection {x,y,opacity,conic.x | conic.y,conic.z,r,g | b,gid,0,0}
  *   status_out (2) int32: [0] = n_isect, [1] = 1 if n_isect > capacity (outputs truncated; retry with more).
  * Requires all depths == 0 (true for both 2D projections). n_isect < 2^30. */
@@ -120,8 +122,9 @@ int gi2d_raster_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, co
                         float *final_Ts, int *final_idx, cudaStream_t stream);
 
 /* Same over the packed records of gi2d_bin_fused (bulk-TMA staging).  If d_status != NULL and d_status[0] == 0 the
- * image is filled with background[0..2], which is what rasterize_sum.py:121-129 returns for zero intersections. */
-int gi2d_raster_sum_fwd_packed(int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
+ * image is filled with background[0..2], which is what rasterize_sum.py:121-129 returns for zero intersections.
+ * Also rewrites the (INT_MAX, 0) markers of empty tiles in tile_bins to (0, 0). */
+int gi2d_raster_sum_fwd_packed(int TX, int TY, int W, int H, int *tile_bins, const float *packed,
                                const int *d_status, const float *background, float *out_img, float *final_Ts,
                                int *final_idx, cudaStream_t stream);
 
