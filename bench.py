@@ -268,8 +268,8 @@ def kernel_rooflines(step, flush, reps, peaks, sm_mhz):
         n_isect = int(r["status"][0].item())
         E = count_evals(r["tile_bins"], H, W)
         v_out = torch.randn(H, W, 3, device=dev) * 1e-3
-        grads = torch.empty(9 * N, device=dev)
-        v_xy, v_conic = grads[:2 * N].view(N, 2), grads[2 * N:5 * N].view(N, 3)
+        grads = torch.empty(N, 12, device=dev)
+        v_xy, v_conic = grads[:, 0:2].contiguous(), grads[:, 2:5].contiguous()
 
         def bwd():
             check(L.gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, r["tile_bins"].data_ptr(), r["packed"].data_ptr(), v_out.data_ptr(),

@@ -23,6 +23,8 @@ _SIGNATURES = {
     "gi2d_project_scale_rot_fwd": (_i, [_i, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_project_cholesky_bwd": (_i, [_i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_project_scale_rot_bwd": (_i, [_i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gi2d_project_cholesky_bwd_packed": (_i, [_i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gi2d_project_scale_rot_bwd_packed": (_i, [_i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_cov2d_bounds": (_i, [_i, _vp, _vp, _vp, _vp]),
     "gi2d_scan_workspace_bytes": (_sz, [_i]),
     "gi2d_scan_tiles": (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp]),

@@ -19,6 +19,7 @@
 // preceding blocks' digit counts, and scatters.  Stability + ascending-gid emission order gives the per-tile
 // ascending-gid order the reference gets from cub (quirk Q2).  All of this is HBM/L2-bound integer work.
 #include "gi2d_common.cuh"
+#include <stdlib.h>
 
 namespace gi2d {
 
@@ -166,13 +167,12 @@ __device__ __forceinline__ void gaussian_bbox(const float *__restrict__ xys, con
 // FUSED additionally emits the compact (tile, gid) pairs and the digit histograms, presets tile_bins to
 // (INT_MAX, 0) for the atomicMin/Max of the last sort pass and writes status_out = {n_isect, overflow}.
 // One Gaussian per thread, SCAN_T threads per block: 70k Gaussians are 69 blocks, so the look-back chain is short.
-constexpr int SCAN_T = 1024;
-template <bool FUSED>
+template <bool FUSED, int SCAN_T>
 __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restrict__ num_tiles_hit, int *__restrict__ cum,
                                                       uint32_t *ctl, uint32_t *scan_state, const float *__restrict__ xys,
                                                       const int *__restrict__ radii, int TX, int TY, int capacity,
                                                       uint32_t *keys_out, int *vals_out, PassPlan plan,
-                                                      int2 *tile_bins_init, int n_bins, int *status_out, int use_ticket) {
+                                                      int2 *tile_bins_init, int n_bins, int *status_out, int use_ticket, int dbg) {
     __shared__ int s_warp[SCAN_T / 32];
     __shared__ int s_bcast[2];
     __shared__ uint32_t s_hist[FUSED ? MAX_PASSES * RADIX : 1];
@@ -204,11 +204,12 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
             if (status_out) { status_out[0] = total; status_out[1] = over; }
         }
     }
-    if (FUSED) {
+    if (FUSED && !(dbg & 1)) {
         int x0 = 0, w = 1, y0 = 0, area = 0;
         if (i < N && cnt > 0) gaussian_bbox(xys, radii, i, TX, TY, x0, w, y0, area);
         warp_emit<0>(cnt, block_excl + incl - cnt, x0, w, y0, area, i, 0, TX, capacity, keys_out, vals_out, s_hist, plan);
         __syncthreads();
+        if (!(dbg & 2))
         for (int k = tid; k < plan.npass * RADIX; k += SCAN_T) {
             const uint32_t c = s_hist[k];
             if (c) atomicAdd(ctl + CTL_HIST + k, c);
@@ -348,13 +349,14 @@ __global__ void __launch_bounds__(SB) onesweep_kernel(const uint32_t *__restrict
         uint32_t excl = 0;
         int pb = vbid - 1;
         while (pb >= 0) {
-            uint32_t w[8];
+            constexpr int LB = 16;                  // predecessor words in flight per step
+            uint32_t w[LB];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) w[j] = (pb - j >= 0) ? ld_volatile(lookback + (size_t)(pb - j) * RADIX + tid) : FLAG_INCL;
+            for (int j = 0; j < LB; ++j) w[j] = (pb - j >= 0) ? ld_volatile(lookback + (size_t)(pb - j) * RADIX + tid) : FLAG_INCL;
             int j = 0;
             bool done = false;
 #pragma unroll
-            for (; j < 8; ++j) {
+            for (; j < LB; ++j) {
                 if ((w[j] >> 30) == 0) break;      // not published yet: re-read from here
                 excl += w[j] & VAL_MASK;
                 if (w[j] & FLAG_INCL) { done = true; break; }
@@ -377,15 +379,19 @@ __global__ void __launch_bounds__(SB) onesweep_kernel(const uint32_t *__restrict
         }
     }
     __syncthreads();
-    for (int li = tid; li < nvalid; li += SB) {
-        const KeyT k = s_keys[li];
-        const int v = s_vals[li];
-        const uint32_t digit = (uint32_t)(((k ^ flip) >> shift) & (KeyT)mask);
-        const uint32_t pos = s_base[digit] + li;
-        vals_out[pos] = v;
-        if (!LAST) {
+    if (!LAST) {
+        for (int li = tid; li < nvalid; li += SB) {
+            const KeyT k = s_keys[li];
+            const uint32_t digit = (uint32_t)(((k ^ flip) >> shift) & (KeyT)mask);
+            const uint32_t pos = s_base[digit] + li;
             keys_out[pos] = k;
-        } else {
+            vals_out[pos] = s_vals[li];
+        }
+    } else {
+        for (int li = tid; li < nvalid; li += SB) {      // bin edges: atomics only matter at block / digit seams
+            const KeyT k = s_keys[li];
+            const uint32_t digit = (uint32_t)(((k ^ flip) >> shift) & (KeyT)mask);
+            const uint32_t pos = s_base[digit] + li;
             const int cur = (int)k;
             if (cur < ps.n_bins) {
                 const bool first = li == 0 || (uint32_t)(((s_keys[li - 1] ^ flip) >> shift) & (KeyT)mask) != digit;
@@ -393,14 +399,25 @@ __global__ void __launch_bounds__(SB) onesweep_kernel(const uint32_t *__restrict
                 if (first || (int)s_keys[li - 1] != cur) atomicMin(ps.tile_bins + 2 * cur, (int)pos);
                 if (last || (int)s_keys[li + 1] != cur) atomicMax(ps.tile_bins + 2 * cur + 1, (int)pos + 1);
             }
-            const size_t g = (size_t)v;
-            const float x = __ldg(ps.xys + 2 * g), y = __ldg(ps.xys + 2 * g + 1);
-            const float cx = __ldg(ps.conics + 3 * g), cy = __ldg(ps.conics + 3 * g + 1), cz = __ldg(ps.conics + 3 * g + 2);
-            const float r = __ldg(ps.colors + 3 * g), gg = __ldg(ps.colors + 3 * g + 1), b = __ldg(ps.colors + 3 * g + 2);
-            const float o = __ldg(ps.opac + g);
-            ps.packed[3 * (size_t)pos + 0] = make_float4(x, y, o, cx);
-            ps.packed[3 * (size_t)pos + 1] = make_float4(cy, cz, r, gg);
-            ps.packed[3 * (size_t)pos + 2] = make_float4(b, __int_as_float(v), 0.f, 0.f);
+        }
+#pragma unroll
+        for (int it = 0; it < ITEMS; ++it) {             // packed records: all gathers of the thread in flight together
+            const int li = tid + it * SB;
+            if (li < nvalid) {
+                const KeyT k = s_keys[li];
+                const int v = s_vals[li];
+                const uint32_t digit = (uint32_t)(((k ^ flip) >> shift) & (KeyT)mask);
+                const uint32_t pos = s_base[digit] + li;
+                vals_out[pos] = v;
+                const size_t g = (size_t)v;
+                const float x = __ldg(ps.xys + 2 * g), y = __ldg(ps.xys + 2 * g + 1);
+                const float cx = __ldg(ps.conics + 3 * g), cy = __ldg(ps.conics + 3 * g + 1), cz = __ldg(ps.conics + 3 * g + 2);
+                const float r = __ldg(ps.colors + 3 * g), gg = __ldg(ps.colors + 3 * g + 1), b = __ldg(ps.colors + 3 * g + 2);
+                const float o = __ldg(ps.opac + g);
+                __stcs(ps.packed + 3 * (size_t)pos + 0, make_float4(x, y, o, cx));
+                __stcs(ps.packed + 3 * (size_t)pos + 1, make_float4(cy, cz, r, gg));
+                __stcs(ps.packed + 3 * (size_t)pos + 2, make_float4(b, __int_as_float(v), 0.f, 0.f));
+            }
         }
     }
 }
@@ -441,8 +458,21 @@ static PassPlan make_plan(int lo_bit, int hi_bit) {   // sort key bits [lo_bit, 
     return p;
 }
 
-constexpr int SORT_ITEMS32 = 16, SORT_TILE32 = SB * SORT_ITEMS32;   // uint32 keys: 4096 per block (41 KB shared)
-constexpr int SORT_ITEMS64 = 8, SORT_TILE64 = SB * SORT_ITEMS64;    // int64 keys: 2048 per block (33 KB shared)
+constexpr int SORT_ITEMS64 = 8, SORT_TILE64 = SB * SORT_ITEMS64;    // int64 keys (staged path): 2048 per block
+
+// Launch shapes of the fused chain.  Everything here is latency-bound at GaussianImage sizes (the whole chain moves a
+// few MB), so the shapes trade look-back chain length against per-block serial work; defaults were picked from
+// measurements on B200 (profiles/), and can be overridden for experiments through the environment.
+struct Tuning { int scan_t, pass_items, last_items; };
+static int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+static const Tuning &tuning() {
+    static Tuning t = {env_int("GI2D_SCAN_T", 1024), env_int("GI2D_PASS_ITEMS", 4), env_int("GI2D_LAST_ITEMS", 4)};
+    return t;
+}
+constexpr int MIN_SCAN_T = 256, MIN_SORT_TILE = SB * 4;
 
 // Look-back order may be blockIdx order when every block of the grid is resident at once (no ticket atomics).
 template <typename K>
@@ -453,8 +483,16 @@ static bool all_resident(K kernel, int threads, int grid) {
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
-    int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess) return false;
+    static const void *keys[64];
+    static int vals[64], used = 0;          // tiny cache keyed by kernel address (the query costs microseconds)
+    const void *key = reinterpret_cast<const void *>(kernel);
+    int per_sm = -1;
+    for (int i = 0; i < used; ++i)
+        if (keys[i] == key) per_sm = vals[i];
+    if (per_sm < 0) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess) per_sm = 0;
+        if (used < 64) { keys[used] = key; vals[used] = per_sm; ++used; }
+    }
     return grid <= per_sm * sms;
 }
 
@@ -465,8 +503,8 @@ struct FusedLayout {          // carve-up of the caller's workspace for gi2d_bin
 static FusedLayout fused_layout(int N, int T, int capacity) {
     FusedLayout L;
     L.npass = make_plan(0, ceil_log2(T > 1 ? T : 2)).npass;
-    L.scan_blocks = (N + SCAN_T - 1) / SCAN_T;
-    L.sort_blocks = (capacity + SORT_TILE32 - 1) / SORT_TILE32;
+    L.scan_blocks = (N + MIN_SCAN_T - 1) / MIN_SCAN_T;                 // sized for the smallest block shapes
+    L.sort_blocks = (capacity + MIN_SORT_TILE - 1) / MIN_SORT_TILE;
     size_t o = 0;
     L.ctl = o; o += align_up(sizeof(uint32_t) * CTL_WORDS, 256);
     L.scan_state = o; o += align_up(sizeof(uint32_t) * (size_t)L.scan_blocks, 256);
@@ -488,7 +526,7 @@ extern "C" {
 // ---- staged, reference-typed entry points ------------------------------------------------------------------------
 
 size_t gi2d_scan_workspace_bytes(int N) {
-    return align_up(sizeof(uint32_t) * CTL_WORDS, 256) + align_up(sizeof(uint32_t) * (size_t)((N + SCAN_T - 1) / SCAN_T), 256);
+    return align_up(sizeof(uint32_t) * CTL_WORDS, 256) + align_up(sizeof(uint32_t) * (size_t)((N + 1023) / 1024), 256);
 }
 
 // compute_cumulative_intersects (utils.py:99-118): cum (N,) int32 inclusive; the total is written to *total_out
@@ -503,10 +541,10 @@ int gi2d_scan_tiles(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *to
     cudaMemsetAsync(ws, 0, need, stream);
     PassPlan none;
     none.npass = 0;
-    const int grid = (N + SCAN_T - 1) / SCAN_T;
-    const int ticket = all_resident(scan_kernel<false>, SCAN_T, grid) ? 0 : 1;
-    scan_kernel<false><<<grid, SCAN_T, 0, stream>>>(N, num_tiles_hit, cum_tiles_hit, ctl, state, nullptr, nullptr, 0, 0, 0, nullptr,
-                                                   nullptr, none, nullptr, 0, nullptr, ticket);
+    const int grid = (N + 1023) / 1024;
+    const int ticket = all_resident(scan_kernel<false, 1024>, 1024, grid) ? 0 : 1;
+    scan_kernel<false, 1024><<<grid, 1024, 0, stream>>>(N, num_tiles_hit, cum_tiles_hit, ctl, state, nullptr, nullptr, 0, 0, 0, nullptr,
+                                                   nullptr, none, nullptr, 0, nullptr, ticket, 0);
     if (total_out) cudaMemcpyAsync(total_out, ctl + CTL_N, sizeof(int), cudaMemcpyDefault, stream);
     return cuda_status();
 }
@@ -615,10 +653,18 @@ int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, co
     // values ping-pong between gids_sorted and vals_b; start so that the last pass lands in gids_sorted
     int *v0 = (plan.npass % 2 == 0) ? gids_sorted : vals_b;
     uint32_t *k0 = keys_a;
-    const int scan_ticket = all_resident(scan_kernel<true>, SCAN_T, L.scan_blocks) ? 0 : 1;
-    scan_kernel<true><<<L.scan_blocks, SCAN_T, 0, stream>>>(N, num_tiles_hit, nullptr, ctl, scan_state, xys, radii, TX, TY, capacity, k0,
-                                                           v0, plan, reinterpret_cast<int2 *>(tile_bins), T, status_out, scan_ticket);
-    const int sort_ticket = all_resident(onesweep_kernel<uint32_t, SORT_ITEMS32, true>, SB, L.sort_blocks) ? 0 : 1;
+    const Tuning &tn = tuning();
+    int2 *bins2 = reinterpret_cast<int2 *>(tile_bins);
+#define GI2D_SCAN(NT)                                                                                                      \
+    {                                                                                                                      \
+        const int grid = (N + NT - 1) / NT;                                                                                \
+        const int ticket = all_resident(scan_kernel<true, NT>, NT, grid) ? 0 : 1;                                          \
+        scan_kernel<true, NT><<<grid, NT, 0, stream>>>(N, num_tiles_hit, nullptr, ctl, scan_state, xys, radii, TX, TY,     \
+                                                       capacity, k0, v0, plan, bins2, T, status_out, ticket, env_int("GI2D_DBG", 0)); \
+    }
+    if (tn.scan_t == 256) GI2D_SCAN(256) else if (tn.scan_t == 512) GI2D_SCAN(512) else GI2D_SCAN(1024)
+#undef GI2D_SCAN
+    if (env_int("GI2D_DBG", 0) & 4) return cuda_status();      // experiments: scan kernel only
     PackSrc none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
     PackSrc ps{xys, conics, colors, opacities, reinterpret_cast<float4 *>(packed), tile_bins, T};
     const uint32_t *src_k = k0;
@@ -627,12 +673,22 @@ int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, co
         uint32_t *dst_k = (src_k == keys_a) ? keys_b : keys_a;
         int *dst_v = (src_v == gids_sorted) ? vals_b : gids_sorted;
         uint32_t *lb = lookback + (size_t)p * L.sort_blocks * RADIX;
-        if (p == plan.npass - 1)
-            onesweep_kernel<uint32_t, SORT_ITEMS32, true><<<L.sort_blocks, SB, 0, stream>>>(
-                ctl + CTL_N, 0, capacity, src_k, src_v, dst_k, dst_v, ctl, lb, p, plan.shift[p], plan.bits[p], 0u, sort_ticket, ps);
-        else
-            onesweep_kernel<uint32_t, SORT_ITEMS32, false><<<L.sort_blocks, SB, 0, stream>>>(
-                ctl + CTL_N, 0, capacity, src_k, src_v, dst_k, dst_v, ctl, lb, p, plan.shift[p], plan.bits[p], 0u, sort_ticket, none);
+        const bool last = p == plan.npass - 1;
+#define GI2D_SWEEP(ITEMS, LASTF, PS)                                                                                       \
+    {                                                                                                                      \
+        const int grid = (capacity + SB * ITEMS - 1) / (SB * ITEMS);                                                       \
+        const int ticket = all_resident(onesweep_kernel<uint32_t, ITEMS, LASTF>, SB, grid) ? 0 : 1;                        \
+        onesweep_kernel<uint32_t, ITEMS, LASTF><<<grid, SB, 0, stream>>>(ctl + CTL_N, 0, capacity, src_k, src_v, dst_k,     \
+                                                                        dst_v, ctl, lb, p, plan.shift[p], plan.bits[p], 0u, \
+                                                                        ticket, PS);                                       \
+    }
+        const int items = last ? tn.last_items : tn.pass_items;
+        if (last) {
+            if (items == 4) GI2D_SWEEP(4, true, ps) else if (items == 8) GI2D_SWEEP(8, true, ps) else GI2D_SWEEP(16, true, ps)
+        } else {
+            if (items == 4) GI2D_SWEEP(4, false, none) else if (items == 8) GI2D_SWEEP(8, false, none) else GI2D_SWEEP(16, false, none)
+        }
+#undef GI2D_SWEEP
         src_k = dst_k;
         src_v = dst_v;
     }

@@ -129,14 +129,14 @@ __global__ void __launch_bounds__(PB) project_bwd_kernel(int N, const float *__r
                                                          const float *__restrict__ v_xy, const float *__restrict__ v_conic,
                                                          float *__restrict__ v_cov2d, float *__restrict__ v_mean2d,
                                                          float *__restrict__ out3, float *__restrict__ out2,
-                                                         float *__restrict__ out1) {
+                                                         float *__restrict__ out1, const float4 *__restrict__ g12) {
     __shared__ __align__(16) float sA[PB * 3];   // conics, then v_cov2d
     __shared__ __align__(16) float sB[PB * 3];   // v_conic, then v_L
     __shared__ __align__(16) float sC[PB * 3];   // L
     const int base = blockIdx.x * PB, tid = threadIdx.x, i = base + tid;
     const int nb = min(PB, N - base);
     stage_in3<VEC>(sA, conics, base, nb);
-    stage_in3<VEC>(sB, v_conic, base, nb);
+    if (!g12) stage_in3<VEC>(sB, v_conic, base, nb);
     if (MODE == 0) stage_in3<VEC>(sC, p3, base, nb);
     __syncthreads();
     float3 G = make_float3(0.f, 0.f, 0.f), o3 = make_float3(0.f, 0.f, 0.f);
@@ -144,11 +144,18 @@ __global__ void __launch_bounds__(PB) project_bwd_kernel(int N, const float *__r
         float2 vm = make_float2(0.f, 0.f), o2 = make_float2(0.f, 0.f);
         float o1 = 0.f;
         if (__ldg(radii + i) > 0) {
-            G = conic_vjp(make_float3(sA[3 * tid], sA[3 * tid + 1], sA[3 * tid + 2]),
-                          make_float3(sB[3 * tid], sB[3 * tid + 1], sB[3 * tid + 2]));
             float vx, vy;
-            if (VEC) { const float2 v = __ldg(reinterpret_cast<const float2 *>(v_xy) + i); vx = v.x; vy = v.y; }
-            else { vx = __ldg(v_xy + 2 * (size_t)i); vy = __ldg(v_xy + 2 * (size_t)i + 1); }
+            float3 vc;
+            if (g12) {      // (N,12) rows of gi2d_raster_sum_bwd_packed: {v_xy.x, v_xy.y, v_conic.x, v_conic.y | v_conic.z, ...}
+                const float4 a = __ldg(g12 + 3 * (size_t)i);
+                vx = a.x; vy = a.y;
+                vc = make_float3(a.z, a.w, __ldg(reinterpret_cast<const float *>(g12) + 12 * (size_t)i + 4));
+            } else {
+                vc = make_float3(sB[3 * tid], sB[3 * tid + 1], sB[3 * tid + 2]);
+                if (VEC) { const float2 v = __ldg(reinterpret_cast<const float2 *>(v_xy) + i); vx = v.x; vy = v.y; }
+                else { vx = __ldg(v_xy + 2 * (size_t)i); vy = __ldg(v_xy + 2 * (size_t)i + 1); }
+            }
+            G = conic_vjp(make_float3(sA[3 * tid], sA[3 * tid + 1], sA[3 * tid + 2]), vc);
             vm = make_float2(vx * hw, vy * hh);                          // backward2d.cu:48-49
             if (MODE == 0) {
                 const float l11 = sC[3 * tid], l21 = sC[3 * tid + 1], l22 = sC[3 * tid + 2];
@@ -261,9 +268,9 @@ int gi2d_project_cholesky_bwd(int N, const float *L, int H, int W, const int *ra
     const bool vec = aligned16(L) && aligned16(conics) && aligned16(v_xy) && aligned16(v_conic) && aligned16(v_mean2d) &&
                      aligned16(v_L) && (v_cov2d == nullptr || aligned16(v_cov2d));
     if (vec)
-        project_bwd_kernel<0, true><<<grid, PB, 0, stream>>>(N, L, nullptr, nullptr, hw, hh, radii, conics, v_xy, v_conic, v_cov2d, v_mean2d, v_L, nullptr, nullptr);
+        project_bwd_kernel<0, true><<<grid, PB, 0, stream>>>(N, L, nullptr, nullptr, hw, hh, radii, conics, v_xy, v_conic, v_cov2d, v_mean2d, v_L, nullptr, nullptr, nullptr);
     else
-        project_bwd_kernel<0, false><<<grid, PB, 0, stream>>>(N, L, nullptr, nullptr, hw, hh, radii, conics, v_xy, v_conic, v_cov2d, v_mean2d, v_L, nullptr, nullptr);
+        project_bwd_kernel<0, false><<<grid, PB, 0, stream>>>(N, L, nullptr, nullptr, hw, hh, radii, conics, v_xy, v_conic, v_cov2d, v_mean2d, v_L, nullptr, nullptr, nullptr);
     return cuda_status();
 }
 
@@ -277,9 +284,40 @@ int gi2d_project_scale_rot_bwd(int N, const float *scales2d, const float *rotati
     const bool vec = aligned16(scales2d) && aligned16(conics) && aligned16(v_xy) && aligned16(v_conic) &&
                      aligned16(v_mean2d) && aligned16(v_scale) && (v_cov2d == nullptr || aligned16(v_cov2d));
     if (vec)
-        project_bwd_kernel<1, true><<<grid, PB, 0, stream>>>(N, nullptr, scales2d, rotation, hw, hh, radii, conics, v_xy, v_conic, v_cov2d, v_mean2d, nullptr, v_scale, v_rot);
+        project_bwd_kernel<1, true><<<grid, PB, 0, stream>>>(N, nullptr, scales2d, rotation, hw, hh, radii, conics, v_xy, v_conic, v_cov2d, v_mean2d, nullptr, v_scale, v_rot, nullptr);
     else
-        project_bwd_kernel<1, false><<<grid, PB, 0, stream>>>(N, nullptr, scales2d, rotation, hw, hh, radii, conics, v_xy, v_conic, v_cov2d, v_mean2d, nullptr, v_scale, v_rot);
+        project_bwd_kernel<1, false><<<grid, PB, 0, stream>>>(N, nullptr, scales2d, rotation, hw, hh, radii, conics, v_xy, v_conic, v_cov2d, v_mean2d, nullptr, v_scale, v_rot, nullptr);
+    return cuda_status();
+}
+
+// The same two backward passes reading v_xy / v_conic straight from the (N,12) gradient rows written by
+// gi2d_raster_sum_bwd_packed (no intermediate (N,2)/(N,3) tensors).
+int gi2d_project_cholesky_bwd_packed(int N, const float *L, int H, int W, const int *radii, const float *conics,
+                                     const float *grads12, float *v_mean2d, float *v_L, cudaStream_t stream) {
+    if (N < 0 || H <= 0 || W <= 0 || !aligned16(grads12)) return GI2D_ERR_INVALID;
+    if (N == 0) return GI2D_OK;
+    const float hw = 0.5f * (float)(unsigned)W, hh = 0.5f * (float)(unsigned)H;
+    const int grid = (N + PB - 1) / PB;
+    const float4 *g = reinterpret_cast<const float4 *>(grads12);
+    if (aligned16(L) && aligned16(conics) && aligned16(v_mean2d) && aligned16(v_L))
+        project_bwd_kernel<0, true><<<grid, PB, 0, stream>>>(N, L, nullptr, nullptr, hw, hh, radii, conics, nullptr, nullptr, nullptr, v_mean2d, v_L, nullptr, nullptr, g);
+    else
+        project_bwd_kernel<0, false><<<grid, PB, 0, stream>>>(N, L, nullptr, nullptr, hw, hh, radii, conics, nullptr, nullptr, nullptr, v_mean2d, v_L, nullptr, nullptr, g);
+    return cuda_status();
+}
+
+int gi2d_project_scale_rot_bwd_packed(int N, const float *scales2d, const float *rotation, int H, int W, const int *radii,
+                                      const float *conics, const float *grads12, float *v_mean2d, float *v_scale,
+                                      float *v_rot, cudaStream_t stream) {
+    if (N < 0 || H <= 0 || W <= 0 || !aligned16(grads12)) return GI2D_ERR_INVALID;
+    if (N == 0) return GI2D_OK;
+    const float hw = 0.5f * (float)(unsigned)W, hh = 0.5f * (float)(unsigned)H;
+    const int grid = (N + PB - 1) / PB;
+    const float4 *g = reinterpret_cast<const float4 *>(grads12);
+    if (aligned16(scales2d) && aligned16(conics) && aligned16(v_mean2d) && aligned16(v_scale))
+        project_bwd_kernel<1, true><<<grid, PB, 0, stream>>>(N, nullptr, scales2d, rotation, hw, hh, radii, conics, nullptr, nullptr, nullptr, v_mean2d, nullptr, v_scale, v_rot, g);
+    else
+        project_bwd_kernel<1, false><<<grid, PB, 0, stream>>>(N, nullptr, scales2d, rotation, hw, hh, radii, conics, nullptr, nullptr, nullptr, v_mean2d, nullptr, v_scale, v_rot, g);
     return cuda_status();
 }
 

@@ -11,10 +11,10 @@
 //     removes pairs the reference rejects, so no output bit changes;
 //   * forward: pixel-parallel, a warp owns an 8x4 pixel block and walks only the records whose extent touches
 //     that block (per-warp compacted index list);
-//   * backward: row-parallel over the records' visible rectangles -- a thread owns one pixel row of one record,
-//     keeps the 9 partial gradients in registers, combines rows in shared memory and issues one set of 9 atomic
-//     adds per (tile, Gaussian); no shuffle reductions.  (The sum rasterizer has no transmittance chain, so the
-//     order over pixels is free.)
+//   * backward: unit-parallel over the records' visible rectangles -- a thread owns one aligned group of 4 pixels
+//     of one record, partial gradients are combined per record through shared memory with plain stores, and one
+//     set of (vector) reductions per (tile, Gaussian) goes to global memory; no shuffle reductions.  (The sum
+//     rasterizer has no transmittance chain, so the order over pixels is free.)
 // Per-pair arithmetic up to the two comparisons is the reference's instruction sequence (gi2d_common.cuh).
 // FP32-pipe bound; no tensor cores (not a dense contraction).
 #include "gi2d_common.cuh"
@@ -158,23 +158,31 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
     }
 }
 
-// Backward.  Work item = one pixel ROW of one staged record's visible rectangle ("row-parallel"): the 256 threads
-// of the CTA walk the flattened list of rows of all records of the tile, so lanes stay busy regardless of how the
-// records' footprints differ; a thread accumulates its row's 9 partial gradients in registers, adds them to the
-// CTA's shared accumulators (one slot set per record) and at the end each record issues ONE set of 9 global atomic
-// adds per tile.  No warp-shuffle reductions, no per-pixel atomics.
-template <bool TMA>
+// Backward.  Work unit = one ALIGNED GROUP OF 4 PIXELS of one row of one staged record's visible rectangle.  The
+// 256 threads of the CTA walk the flattened list of units of all records of the tile, 256 units per round, so every
+// lane always has exactly four (masked) pixel evaluations to do, whatever the records' footprints are.  A unit's 9
+// partial gradients go to shared memory with plain stores; the thread that owns a record then adds up the partials
+// of that record's units of the round in registers.  No shuffle reductions, no shared-memory atomics; per
+// (tile, Gaussian) one set of global reductions -- three 16-byte vector `red.global.add.v4.f32` in the packed layout.
+__device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+struct GradOut {            // VEC12: g12 = (N,12) rows {v_xy.x, v_xy.y, v_conic.xyz, v_colors.rgb, v_opacity, 0, 0, 0}
+    float *g12;
+    float *v_xy, *v_conic, *v_colors, *v_opacity;
+};
+
+template <bool TMA, bool VEC12>
 __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, const int *__restrict__ tile_bins,
                                                         const float4 *__restrict__ packed, GatherSrc src,
-                                                        const float *__restrict__ v_out, float *__restrict__ v_xy,
-                                                        float *__restrict__ v_conic, float *__restrict__ v_colors,
-                                                        float *__restrict__ v_opacity) {
+                                                        const float *__restrict__ v_out, GradOut out) {
     __shared__ __align__(128) float4 s_rec[RB * 3];
-    __shared__ __align__(16) float4 s_vout[GI2D_TILE_PIX];
-    __shared__ float s_acc[9][RB];                   // [component][record]: conflict-free for per-record access
-    __shared__ uint32_t s_rect[RB];                  // lx0 | lx1<<8 | ly0<<16 | rows<<24
-    __shared__ uint16_t s_pref[RB];                  // exclusive prefix of the row counts
-    __shared__ uint8_t s_owner[RB * GI2D_TILE];      // flattened row index -> record
+    __shared__ __align__(16) float s_v[3][GI2D_TILE_PIX];      // upstream gradient, one plane per channel
+    __shared__ float s_part[9][RB];                            // per-unit partials of the current round
+    __shared__ uint32_t s_rect[RB];                            // x0 | x1<<4 | y0<<8 | g0<<12 | segs<<14 | rows<<17
+    __shared__ uint16_t s_pref[RB];                            // exclusive prefix of the unit counts
+    __shared__ uint8_t s_owner[RB];                            // unit of the current round -> record
     __shared__ int s_warp[RB / 32];
     __shared__ __align__(8) uint64_t s_bar;
 
@@ -188,24 +196,30 @@ __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, co
     if (cnt <= 0) return;
 
     {   // the tile of upstream gradients, zero outside the image (such pixels then contribute exact zeros)
-        const int lx = tid & 15, ly = tid >> 4;
-        const int j = tx0 + lx, i = ty0 + ly;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int j = tx0 + (tid & 15), i = ty0 + (tid >> 4);
+        float vr = 0.f, vg = 0.f, vb = 0.f;
         if (i < H && j < W) {
             const size_t pix = (size_t)i * W + j;
-            v.x = __ldg(v_out + 3 * pix); v.y = __ldg(v_out + 3 * pix + 1); v.z = __ldg(v_out + 3 * pix + 2);
+            vr = __ldg(v_out + 3 * pix); vg = __ldg(v_out + 3 * pix + 1); vb = __ldg(v_out + 3 * pix + 2);
         }
-        s_vout[tid] = v;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) s_acc[k][tid] = 0.f;
+        s_v[0][tid] = vr; s_v[1][tid] = vg; s_v[2][tid] = vb;
     }
     stage_records<TMA>(s_rec, &s_bar, packed, src, lo, cnt);
 
-    // per record: visible rectangle and its row count; block-wide exclusive scan of the row counts
-    int rows = 0, lx0 = 0, lx1 = 0, ly0 = 0, ly1 = 0;
-    if (tid < cnt && record_rect(s_rec[3 * tid], s_rec[3 * tid + 1], tx0, ty0, lx0, lx1, ly0, ly1)) rows = ly1 - ly0 + 1;
-    s_rect[tid] = (uint32_t)lx0 | ((uint32_t)lx1 << 8) | ((uint32_t)ly0 << 16) | ((uint32_t)rows << 24);
-    int incl = rows;
+    // per record: visible rectangle -> rows x aligned 4-pixel groups = units; block-wide exclusive scan of the unit counts
+    int units = 0;
+    {
+        int lx0 = 0, lx1 = 0, ly0 = 0, ly1 = 0;
+        uint32_t rect = 0;
+        if (tid < cnt && record_rect(s_rec[3 * tid], s_rec[3 * tid + 1], tx0, ty0, lx0, lx1, ly0, ly1)) {
+            const int g0 = lx0 >> 2, segs = (lx1 >> 2) - g0 + 1, rows = ly1 - ly0 + 1;
+            units = rows * segs;
+            rect = (uint32_t)lx0 | ((uint32_t)lx1 << 4) | ((uint32_t)ly0 << 8) | ((uint32_t)g0 << 12) | ((uint32_t)segs << 14) |
+                   ((uint32_t)rows << 17);
+        }
+        s_rect[tid] = rect;
+    }
+    int incl = units;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const int t = __shfl_up_sync(0xffffffffu, incl, d);
@@ -213,71 +227,94 @@ __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, co
     }
     if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    int wbase = 0;
+    int wbase = 0, total = 0;
 #pragma unroll
-    for (int w = 0; w < RB / 32; ++w) wbase += (w < warp) ? s_warp[w] : 0;
-    int total = 0;
-#pragma unroll
-    for (int w = 0; w < RB / 32; ++w) total += s_warp[w];
-    const int excl = wbase + incl - rows;
-    s_pref[tid] = (uint16_t)excl;
-    for (int q = 0; q < rows; ++q) s_owner[excl + q] = (uint8_t)tid;
-    __syncthreads();
-
-    for (int r = tid; r < total; r += RB) {
-        const int t = s_owner[r];
-        const uint32_t rect = s_rect[t];
-        const int x0 = rect & 0xff, x1 = (rect >> 8) & 0xff;
-        const int ly = (int)((rect >> 16) & 0xff) + (r - (int)s_pref[t]);
-        const float4 A = s_rec[3 * t], B = s_rec[3 * t + 1];
-        const float cb = s_rec[3 * t + 2].x;
-        const float x = A.x, opac = A.z, cx = A.w, cy = B.x, cz = B.y, cr = B.z, cg = B.w;
-        const float dy = fsub(A.y, (float)(ty0 + ly));
-        const float t3 = fmul(dy, fmul(cz, dy));
-        const float cydy = cy * dy, czdy = cz * dy;
-        float a_r = 0.f, a_g = 0.f, a_b = 0.f, a_cxx = 0.f, a_cxy = 0.f, a_cyy = 0.f, a_x = 0.f, a_y = 0.f, a_o = 0.f;
-        float fx = (float)(tx0 + x0);
-        const float4 *vrow = s_vout + ly * GI2D_TILE;
-        for (int lx = x0; lx <= x1; ++lx, fx += 1.f) {
-            const float dx = fsub(x, fx);
-            const float q = ffma(dx, fmul(cx, dx), t3);
-            const float sigma = ffma(dy, fmul(cy, dx), fmul(q, 0.5f));
-            float vis = exp_neg(sigma);
-            const float raw = fmul(opac, vis);
-            const bool valid = !(sigma < 0.f) && !(fminf(raw, 1.f) < GI2D_ALPHA_MIN);     // backward.cu:806-808
-            const float alpha = valid ? fminf(raw, 1.f) : 0.f;
-            vis = valid ? vis : 0.f;
-            const float4 vo = vrow[lx];
-            a_r = fmaf(alpha, vo.x, a_r); a_g = fmaf(alpha, vo.y, a_g); a_b = fmaf(alpha, vo.z, a_b);   // backward.cu:814
-            const float v_alpha = fmaf(cr, vo.x, fmaf(cg, vo.y, cb * vo.z));                          // :818-820
-            const float v_sigma = -(opac * vis) * v_alpha;                                            // :822
-            const float hs = 0.5f * v_sigma;
-            const float hdx = hs * dx;
-            a_cxx = fmaf(hdx, dx, a_cxx); a_cxy = fmaf(hdx, dy, a_cxy); a_cyy = fmaf(hs * dy, dy, a_cyy);   // :823-825
-            a_x = fmaf(v_sigma, fmaf(cx, dx, cydy), a_x);                                             // :826-827
-            a_y = fmaf(v_sigma, fmaf(cy, dx, czdy), a_y);
-            a_o = fmaf(vis, v_alpha, a_o);                                                            // :828
-        }
-        if (a_r != 0.f || a_g != 0.f || a_b != 0.f || a_o != 0.f || a_x != 0.f || a_y != 0.f || a_cxx != 0.f || a_cxy != 0.f ||
-            a_cyy != 0.f) {
-            atomicAdd(&s_acc[0][t], a_x); atomicAdd(&s_acc[1][t], a_y);
-            atomicAdd(&s_acc[2][t], a_cxx); atomicAdd(&s_acc[3][t], a_cxy); atomicAdd(&s_acc[4][t], a_cyy);
-            atomicAdd(&s_acc[5][t], a_r); atomicAdd(&s_acc[6][t], a_g); atomicAdd(&s_acc[7][t], a_b);
-            atomicAdd(&s_acc[8][t], a_o);
-        }
+    for (int w = 0; w < RB / 32; ++w) {
+        const int c = s_warp[w];
+        wbase += (w < warp) ? c : 0;
+        total += c;
     }
-    __syncthreads();
-    if (tid >= cnt || rows == 0) return;
-    float g[9];
+    const int ubeg = wbase + incl - units, uend = ubeg + units;     // this record's units in the flattened list
+    s_pref[tid] = (uint16_t)ubeg;
+
+    float acc[9];
+#pragma unroll
+    for (int c = 0; c < 9; ++c) acc[c] = 0.f;
+
+    for (int base = 0; base < total; base += RB) {
+        // (a) owners of this round's units
+        for (int u = max(ubeg, base); u < min(uend, base + RB); ++u) s_owner[u - base] = (uint8_t)tid;
+        __syncthreads();
+        // (b) one unit per thread: four masked pixel evaluations
+        if (base + tid < total) {
+            const int t = s_owner[tid];
+            const uint32_t rect = s_rect[t];
+            const int x0 = rect & 15, x1 = (rect >> 4) & 15, y0 = (rect >> 8) & 15, g0 = (rect >> 12) & 3, segs = (rect >> 14) & 7;
+            const int k = base + tid - (int)s_pref[t];
+            const int row = segs == 1 ? k : segs == 2 ? (k >> 1) : segs == 4 ? (k >> 2) : ((k * 43) >> 7);
+            const int g = g0 + (k - row * segs);
+            const int ly = y0 + row;
+            const float4 A = s_rec[3 * t], B = s_rec[3 * t + 1];
+            const float cb = s_rec[3 * t + 2].x;
+            const float x = A.x, opac = A.z, cx = A.w, cy = B.x, cz = B.y, cr = B.z, cg = B.w;
+            const float dy = fsub(A.y, (float)(ty0 + ly));
+            const float t3 = fmul(dy, fmul(cz, dy));
+            const float cydy = cy * dy, czdy = cz * dy;
+            const float4 vr4 = reinterpret_cast<const float4 *>(s_v[0])[ly * 4 + g];
+            const float4 vg4 = reinterpret_cast<const float4 *>(s_v[1])[ly * 4 + g];
+            const float4 vb4 = reinterpret_cast<const float4 *>(s_v[2])[ly * 4 + g];
+            const float vr[4] = {vr4.x, vr4.y, vr4.z, vr4.w}, vg[4] = {vg4.x, vg4.y, vg4.z, vg4.w}, vb[4] = {vb4.x, vb4.y, vb4.z, vb4.w};
+            float a_r = 0.f, a_g = 0.f, a_b = 0.f, a_cxx = 0.f, a_cxy = 0.f, a_cyy = 0.f, a_x = 0.f, a_y = 0.f, a_o = 0.f;
+            const float fx0 = (float)(tx0 + 4 * g);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int lx = 4 * g + j;
+                const float dx = fsub(x, fx0 + (float)j);
+                const float q = ffma(dx, fmul(cx, dx), t3);
+                const float sigma = ffma(dy, fmul(cy, dx), fmul(q, 0.5f));
+                float vis = exp_neg(sigma);
+                const float raw = fminf(fmul(opac, vis), 1.f);
+                const bool valid = lx >= x0 && lx <= x1 && !(sigma < 0.f) && !(raw < GI2D_ALPHA_MIN);   // backward.cu:806-808
+                const float alpha = valid ? raw : 0.f;
+                vis = valid ? vis : 0.f;
+                a_r = fmaf(alpha, vr[j], a_r); a_g = fmaf(alpha, vg[j], a_g); a_b = fmaf(alpha, vb[j], a_b);   // backward.cu:814
+                const float v_alpha = fmaf(cr, vr[j], fmaf(cg, vg[j], cb * vb[j]));                          // :818-820
+                const float v_sigma = -(opac * vis) * v_alpha;                                               // :822
+                const float hs = 0.5f * v_sigma;
+                const float hdx = hs * dx;
+                a_cxx = fmaf(hdx, dx, a_cxx); a_cxy = fmaf(hdx, dy, a_cxy); a_cyy = fmaf(hs * dy, dy, a_cyy);   // :823-825
+                a_x = fmaf(v_sigma, fmaf(cx, dx, cydy), a_x);                                                // :826-827
+                a_y = fmaf(v_sigma, fmaf(cy, dx, czdy), a_y);
+                a_o = fmaf(vis, v_alpha, a_o);                                                               // :828
+            }
+            s_part[0][tid] = a_x; s_part[1][tid] = a_y; s_part[2][tid] = a_cxx; s_part[3][tid] = a_cxy; s_part[4][tid] = a_cyy;
+            s_part[5][tid] = a_r; s_part[6][tid] = a_g; s_part[7][tid] = a_b; s_part[8][tid] = a_o;
+        }
+        __syncthreads();
+        // (c) every record adds up its units of this round
+        for (int u = max(ubeg, base) - base; u < min(uend, base + RB) - base; ++u) {
+#pragma unroll
+            for (int c = 0; c < 9; ++c) acc[c] += s_part[c][u];
+        }
+        // the next round's (a) writes s_owner only; its barrier also orders these reads before the next (b)
+    }
+    if (units == 0) return;
     bool any = false;
 #pragma unroll
-    for (int k = 0; k < 9; ++k) { g[k] = s_acc[k][tid]; any |= g[k] != 0.f; }
+    for (int c = 0; c < 9; ++c) any |= acc[c] != 0.f;
     if (!any) return;
-    const int gid = __float_as_int(s_rec[3 * tid + 2].y);
-    atomicAdd(v_xy + 2 * (size_t)gid, g[0]); atomicAdd(v_xy + 2 * (size_t)gid + 1, g[1]);
-    atomicAdd(v_conic + 3 * (size_t)gid, g[2]); atomicAdd(v_conic + 3 * (size_t)gid + 1, g[3]); atomicAdd(v_conic + 3 * (size_t)gid + 2, g[4]);
-    atomicAdd(v_colors + 3 * (size_t)gid, g[5]); atomicAdd(v_colors + 3 * (size_t)gid + 1, g[6]); atomicAdd(v_colors + 3 * (size_t)gid + 2, g[7]);
-    atomicAdd(v_opacity + gid, g[8]);
+    const size_t gid = (size_t)__float_as_int(s_rec[3 * tid + 2].y);
+    if (VEC12) {
+        float *row = out.g12 + 12 * gid;
+        red_add_v4(row, acc[0], acc[1], acc[2], acc[3]);
+        red_add_v4(row + 4, acc[4], acc[5], acc[6], acc[7]);
+        atomicAdd(row + 8, acc[8]);
+    } else {
+        atomicAdd(out.v_xy + 2 * gid, acc[0]); atomicAdd(out.v_xy + 2 * gid + 1, acc[1]);
+        atomicAdd(out.v_conic + 3 * gid, acc[2]); atomicAdd(out.v_conic + 3 * gid + 1, acc[3]); atomicAdd(out.v_conic + 3 * gid + 2, acc[4]);
+        atomicAdd(out.v_colors + 3 * gid, acc[5]); atomicAdd(out.v_colors + 3 * gid + 1, acc[6]); atomicAdd(out.v_colors + 3 * gid + 2, acc[7]);
+        atomicAdd(out.v_opacity + gid, acc[8]);
+    }
 }
 
 static inline int cuda_status() {
@@ -333,19 +370,22 @@ int gi2d_raster_sum_bwd(int N, int TX, int TY, int W, int H, const int *gids_sor
     cudaMemsetAsync(v_colors, 0, sizeof(float) * 3 * (size_t)N, stream);
     cudaMemsetAsync(v_opacity, 0, sizeof(float) * (size_t)N, stream);
     GatherSrc src{gids_sorted, xys, conics, colors, opacities};
-    raster_bwd_kernel<false><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, nullptr, src, v_out, v_xy, v_conic, v_colors, v_opacity);
+    GradOut out{nullptr, v_xy, v_conic, v_colors, v_opacity};
+    raster_bwd_kernel<false, false><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, nullptr, src, v_out, out);
     return cuda_status();
 }
 
-// Backward over the packed records.  `grads` is ONE zero-filled-here buffer of 9*N floats laid out as
-// [v_xy (N,2) | v_conic (N,3) | v_colors (N,3) | v_opacity (N,1)] so a single memset precedes the kernel.
+// Backward over the packed records.  `grads12` is ONE buffer of (N,12) floats, zero-filled here, one 48-byte row
+// per Gaussian: {v_xy.x, v_xy.y, v_conic.x, v_conic.y | v_conic.z, v_colors.r, .g, .b | v_opacity, 0, 0, 0}
+// (16-byte aligned rows so that the kernel can use vector reductions).
 int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
-                               const float *v_out, float *grads, cudaStream_t stream) {
+                               const float *v_out, float *grads12, cudaStream_t stream) {
     if (N <= 0 || TX <= 0 || TY <= 0) return GI2D_ERR_INVALID;
-    cudaMemsetAsync(grads, 0, sizeof(float) * 9 * (size_t)N, stream);
+    if (reinterpret_cast<uintptr_t>(grads12) & 15) return GI2D_ERR_INVALID;
+    cudaMemsetAsync(grads12, 0, sizeof(float) * 12 * (size_t)N, stream);
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
-    raster_bwd_kernel<true><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out,
-                                                      grads, grads + 2 * (size_t)N, grads + 5 * (size_t)N, grads + 8 * (size_t)N);
+    GradOut out{grads12, nullptr, nullptr, nullptr, nullptr};
+    raster_bwd_kernel<true, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out, out);
     return cuda_status();
 }
 

@@ -232,3 +232,43 @@ def rasterize_sum_backward(img_height: int, img_width: int, BLOCK_H: int, BLOCK_
                                         _p(final_idx), _p(v_out), _p(v_xy), _p(v_conic), _p(v_colors), _p(v_opacity),
                                         _stream(dev)), "rasterize_sum_backward")
     return v_xy, v_conic, v_colors, v_opacity
+
+
+def _is_packed_pair(v_xy: Tensor, v_conic: Tensor) -> bool:
+    """True when v_xy (N,2) and v_conic (N,3) are columns 0-1 and 2-4 of one (N,12) gradient buffer written by
+    gi2d_raster_sum_bwd_packed, so the projection backward can read the rows in place."""
+    return (v_xy.is_cuda and v_xy.dtype == torch.float32 and v_conic.dtype == torch.float32
+            and v_xy.dim() == 2 and v_conic.dim() == 2 and v_xy.shape[1] == 2 and v_conic.shape[1] == 3
+            and v_xy.stride() == (12, 1) and v_conic.stride() == (12, 1)
+            and v_conic.data_ptr() == v_xy.data_ptr() + 8 and v_xy.data_ptr() % 16 == 0)
+
+
+def project_backward_autograd(mode: str, num_points: int, params, img_height: int, img_width: int, radii: Tensor,
+                              conics: Tensor, v_xy, v_conic):
+    """Backward of either projection for the autograd Functions: (v_mean2d, v_L) or (v_mean2d, v_scale, v_rot).
+    Skips the v_cov2d output the reference computes and discards, and reads packed gradient rows in place."""
+    N, dev = int(num_points), conics.device
+    if v_xy is None:
+        v_xy = torch.zeros((N, 2), dtype=torch.float32, device=dev)
+    if v_conic is None:
+        v_conic = torch.zeros((N, 3), dtype=torch.float32, device=dev)
+    if not _is_packed_pair(v_xy, v_conic):
+        if mode == "cholesky":
+            return project_gaussians_2d_backward(N, None, params[0], img_height, img_width, radii, conics, v_xy, None, v_conic,
+                                                 want_cov2d=False)[1:]
+        return project_gaussians_2d_scale_rot_backward(N, None, params[0], params[1], img_height, img_width, radii, conics,
+                                                       v_xy, None, v_conic, want_cov2d=False)[1:]
+    with torch.cuda.device(dev):
+        v_mean2d = torch.empty((N, 2), dtype=torch.float32, device=dev)
+        if mode == "cholesky":
+            v_L = torch.empty((N, 3), dtype=torch.float32, device=dev)
+            check(lib().gi2d_project_cholesky_bwd_packed(N, _p(params[0]), img_height, img_width, _p(radii), _p(conics),
+                                                         v_xy.data_ptr(), _p(v_mean2d), _p(v_L), _stream(dev)),
+                  "project_gaussians_2d_backward")
+            return v_mean2d, v_L
+        v_scale = torch.empty((N, 2), dtype=torch.float32, device=dev)
+        v_rot = torch.empty((N, 1), dtype=torch.float32, device=dev)
+        check(lib().gi2d_project_scale_rot_bwd_packed(N, _p(params[0]), _p(params[1]), img_height, img_width, _p(radii),
+                                                      _p(conics), v_xy.data_ptr(), _p(v_mean2d), _p(v_scale), _p(v_rot),
+                                                      _stream(dev)), "project_gaussians_2d_scale_rot_backward")
+        return v_mean2d, v_scale, v_rot

@@ -47,14 +47,13 @@ class _ProjectGaussians2d(Function):
         ctx.img_height, ctx.img_width, ctx.num_points = img_height, img_width, num_points
         ctx.save_for_backward(means2d, L_elements, radii, conics)
         ctx.mark_non_differentiable(radii, num_tiles_hit)
+        ctx.set_materialize_grads(False)      # v_depths etc. arrive as None instead of freshly filled zero tensors
         _tag_zero_depth(depths)
         return xys, depths, radii, conics, num_tiles_hit
 
     @staticmethod
     def backward(ctx, v_xys, v_depths, v_radii, v_conics, v_num_tiles_hit):
         means2d, L_elements, radii, conics = ctx.saved_tensors
-        _, v_mean2d, v_L = _C.project_gaussians_2d_backward(
-            ctx.num_points, means2d, L_elements, ctx.img_height, ctx.img_width, radii, conics, v_xys, v_depths, v_conics,
-            want_cov2d=False,   # the reference computes v_cov2d and discards it (project_gaussians_2d.py:114,128-141)
-        )
+        v_mean2d, v_L = _C.project_backward_autograd("cholesky", ctx.num_points, (L_elements,), ctx.img_height,
+                                                     ctx.img_width, radii, conics, v_xys, v_conics)
         return v_mean2d, v_L, None, None, None, None

@@ -40,14 +40,13 @@ class _ProjectGaussians2dScaleRot(Function):
         ctx.img_height, ctx.img_width, ctx.num_points = img_height, img_width, num_points
         ctx.save_for_backward(means2d, scales2d, rotation, radii, conics)
         ctx.mark_non_differentiable(radii, num_tiles_hit)
+        ctx.set_materialize_grads(False)
         _tag_zero_depth(depths)
         return xys, depths, radii, conics, num_tiles_hit
 
     @staticmethod
     def backward(ctx, v_xys, v_depths, v_radii, v_conics, v_num_tiles_hit):
         means2d, scales2d, rotation, radii, conics = ctx.saved_tensors
-        _, v_mean2d, v_scale, v_rot = _C.project_gaussians_2d_scale_rot_backward(
-            ctx.num_points, means2d, scales2d, rotation, ctx.img_height, ctx.img_width, radii, conics, v_xys, v_depths,
-            v_conics, want_cov2d=False,
-        )
+        v_mean2d, v_scale, v_rot = _C.project_backward_autograd("scale_rot", ctx.num_points, (scales2d, rotation), ctx.img_height,
+                                                                ctx.img_width, radii, conics, v_xys, v_conics)
         return v_mean2d, v_scale, v_rot, None, None, None, None

@@ -107,6 +107,7 @@ class _RasterizeGaussiansSum(Function):
         H, W = int(img_height), int(img_width)
         TX, TY = (W + 15) // 16, (H + 15) // 16
         ctx.H, ctx.W, ctx.TX, ctx.TY = H, W, TX, TY
+        ctx.set_materialize_grads(False)
         ctx.N = xys.size(0)
         fast = _depths_known_zero(depths) and xys.is_cuda and xys.dtype == torch.float32
         ctx.fast = fast
@@ -123,19 +124,18 @@ class _RasterizeGaussiansSum(Function):
     @staticmethod
     def backward(ctx, v_out_img, v_out_alpha=None):
         N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
+        if v_out_img is None:                   # only out_alpha was used downstream: the reference ignores v_out_alpha (Q7)
+            return (None,) * 13
         if ctx.fast:
             tile_bins, packed = ctx.saved_tensors
             dev = packed.device
             v_out = _C._f32(v_out_img.contiguous(), "v_out_img")
             with torch.cuda.device(dev):
-                grads = torch.empty((9 * N,), dtype=torch.float32, device=dev)
+                grads = torch.empty((N, 12), dtype=torch.float32, device=dev)     # 48-byte rows: vector reductions
                 check(lib().gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(),
                                                        v_out.data_ptr(), grads.data_ptr(), _C._stream(dev)),
                       "rasterize_sum_backward")
-            v_xy = grads[: 2 * N].view(N, 2)
-            v_conic = grads[2 * N: 5 * N].view(N, 3)
-            v_colors = grads[5 * N: 8 * N].view(N, 3)
-            v_opacity = grads[8 * N:].view(N, 1)
+            v_xy, v_conic, v_colors, v_opacity = grads[:, 0:2], grads[:, 2:5], grads[:, 5:8], grads[:, 8:9]
         else:
             gids_sorted, tile_bins, xys, conics, colors, opacity, background, final_Ts, final_idx = ctx.saved_tensors
             if ctx.num_intersects < 1:          # reference :209-213
@@ -147,7 +147,7 @@ class _RasterizeGaussiansSum(Function):
                 v_xy, v_conic, v_colors, v_opacity = _C.rasterize_sum_backward(
                     H, W, 16, 16, gids_sorted, tile_bins, xys, conics, colors, opacity, background, final_Ts, final_idx,
                     v_out_img, v_out_alpha)
-        v_opacity = v_opacity.view(ctx.opacity_shape)
+        v_opacity = v_opacity.reshape(ctx.opacity_shape)
         return (v_xy, None, None, v_conic, None, v_colors, v_opacity, None, None, None, None, None, None)
 
 

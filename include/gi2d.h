@@ -67,6 +67,14 @@ int gi2d_project_scale_rot_bwd(int N, const float *scales2d, const float *rotati
                                const float *conics, const float *v_xy, const float *v_conic, float *v_cov2d,
                                float *v_mean2d, float *v_scale, float *v_rot, cudaStream_t stream);
 
+/* The two projection backward passes reading v_xy / v_conic directly from the (N,12) gradient rows that
+ * gi2d_raster_sum_bwd_packed writes (columns 0-1 and 2-4), i.e. without materialising (N,2)/(N,3) tensors. */
+int gi2d_project_cholesky_bwd_packed(int N, const float *L, int H, int W, const int *radii, const float *conics,
+                                     const float *grads12, float *v_mean2d, float *v_L, cudaStream_t stream);
+int gi2d_project_scale_rot_bwd_packed(int N, const float *scales2d, const float *rotation, int H, int W, const int *radii,
+                                      const float *conics, const float *grads12, float *v_mean2d, float *v_scale,
+                                      float *v_rot, cudaStream_t stream);
+
 /* Replaces compute_cov2d_bounds (ext.cpp:12 -> bindings.cu:21-61).  cov2d (N,3) upper triangle;
  * conics (N,3), radii (N,1) FLOAT (as in the reference). */
 int gi2d_cov2d_bounds(int N, const float *cov2d, float *conics, float *radii, cudaStream_t stream);
@@ -137,9 +145,10 @@ int gi2d_raster_sum_bwd(int N, int TX, int TY, int W, int H, const int *gids_sor
                         const int *final_idx, const float *v_out, float *v_xy, float *v_conic, float *v_colors,
                         float *v_opacity, cudaStream_t stream);
 
-/* Same over the packed records; `grads` is one buffer of 9*N floats: [v_xy | v_conic | v_colors | v_opacity]. */
+/* Same over the packed records; `grads12` is one 16-byte-aligned buffer of (N,12) floats, zeroed by the call, one
+ * 48-byte row per Gaussian: {v_xy.x, v_xy.y, v_conic.x, v_conic.y | v_conic.z, v_colors.rgb | v_opacity, 0, 0, 0}. */
 int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
-                               const float *v_out, float *grads, cudaStream_t stream);
+                               const float *v_out, float *grads12, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

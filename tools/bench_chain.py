@@ -1,0 +1,87 @@
+"""GPU time of the individual stages of one fit step, each captured in its own CUDA graph (so host launch cost is
+excluded) and replayed with an L2 flush in between.  python tools/bench_chain.py [C2]   (env GI2D_* knobs apply)"""
+import statistics
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import torch
+
+import gaussianimage_b200 as G
+from gaussianimage_b200 import cuda as GC
+from gaussianimage_b200._lib import check, lib
+from gaussianimage_b200.synth import make_config
+
+cfg = sys.argv[1] if len(sys.argv) > 1 else "C2"
+s = make_config(cfg)
+d = s.to("cuda:0")
+dev = d.gt.device
+H, W, (TX, TY, _) = s.H, s.W, s.tile_bounds
+N = d.means2d.shape[0]
+L = lib()
+xys, depths, radii, conics, nth = G.project_gaussians_2d(d.means2d, d.cholesky, H, W, s.tile_bounds)
+n = int(nth.sum().item())
+cap = int(n * 1.25) + 1024
+ws_bytes = L.gi2d_bin_fused_workspace_bytes(N, TX, TY, cap)
+ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+gids = torch.empty(cap, dtype=torch.int32, device=dev)
+bins = torch.empty(TX * TY, 2, dtype=torch.int32, device=dev)
+packed = torch.empty(cap * 12, device=dev)
+status = torch.empty(2, dtype=torch.int32, device=dev)
+out = torch.empty(H, W, 3, device=dev)
+bg = torch.ones(3, device=dev)
+v_out = torch.randn(H, W, 3, device=dev) * 1e-3
+grads = torch.empty(N, 12, device=dev)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def binning():
+    check(L.gi2d_bin_fused(N, TX, TY, xys.data_ptr(), radii.data_ptr(), nth.data_ptr(), conics.data_ptr(), d.colors.data_ptr(),
+                           d.opacity.data_ptr(), cap, ws.data_ptr(), ws_bytes, gids.data_ptr(), bins.data_ptr(), packed.data_ptr(),
+                           status.data_ptr(), stream()), "bin")
+
+
+def fwd():
+    check(L.gi2d_raster_sum_fwd_packed(TX, TY, W, H, bins.data_ptr(), packed.data_ptr(), status.data_ptr(), bg.data_ptr(),
+                                       out.data_ptr(), 0, 0, stream()), "fwd")
+
+
+def bwd():
+    check(L.gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, bins.data_ptr(), packed.data_ptr(), v_out.data_ptr(), grads.data_ptr(),
+                                       stream()), "bwd")
+
+
+def pfwd():
+    GC.project_gaussians_2d_forward(N, d.means2d, d.cholesky, H, W, s.tile_bounds)
+
+
+def time_graph(fn, reps=30):
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    for _ in range(3):
+        g.replay()
+    ts = []
+    for _ in range(reps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); g.replay(); b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) * 1e3)
+    return statistics.median(ts), min(ts)
+
+
+binning(); fwd(); bwd()
+torch.cuda.synchronize()
+assert status.tolist() == [n, 0]
+for name, fn in (("binning_chain", binning), ("raster_fwd", fwd), ("raster_bwd", bwd), ("project_fwd", pfwd)):
+    med, mn = time_graph(fn)
+    print(f"{name:16s} median {med:7.2f} us   min {mn:7.2f} us")
