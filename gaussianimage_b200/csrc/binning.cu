@@ -151,13 +151,16 @@ __device__ __forceinline__ void warp_emit(int cnt, int off, int x0, int w, int y
     }
 }
 
+// Tile bbox of Gaussian i, optionally clipped to the tile-row window [wy0, wy1) of a row-sharded render.
 __device__ __forceinline__ void gaussian_bbox(const float *__restrict__ xys, const int *__restrict__ radii, int i, int TX,
-                                              int TY, int &x0, int &w, int &y0, int &area) {
+                                              int TY, int &x0, int &w, int &y0, int &area, int wy0 = 0, int wy1 = 0x7fffffff) {
     x0 = w = y0 = area = 0;
     const int r = __ldg(radii + i);
     if (r <= 0) return;                                   // forward.cu:113-114
     int x1, y1;
     tile_bbox(__ldg(xys + 2 * (size_t)i), __ldg(xys + 2 * (size_t)i + 1), (float)r, TX, TY, x0, x1, y0, y1);
+    y0 = max(y0, wy0);
+    y1 = min(y1, wy1);
     w = x1 - x0;
     area = max(0, w) * max(0, y1 - y0);
     if (w <= 0) { w = 1; area = 0; }
@@ -172,7 +175,7 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
                                                       uint32_t *ctl, uint32_t *scan_state, const float *__restrict__ xys,
                                                       const int *__restrict__ radii, int TX, int TY, int capacity,
                                                       uint32_t *keys_out, int *vals_out, PassPlan plan,
-                                                      int2 *tile_bins_init, int n_bins, int *status_out, int use_ticket, int dbg) {
+                                                      int2 *tile_bins_init, int n_bins, int *status_out, int use_ticket, int dbg, int wy0, int wy1) {
     __shared__ int s_warp[SCAN_T / 32];
     __shared__ int s_bcast[2];
     __shared__ uint32_t s_hist[FUSED ? MAX_PASSES * RADIX : 1];
@@ -185,7 +188,13 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
     __syncthreads();
     const int vbid = use_ticket ? s_bcast[0] : (int)blockIdx.x;
     const int i = vbid * SCAN_T + tid;
-    const int cnt = i < N ? __ldg(num_tiles_hit + i) : 0;
+    int cnt = i < N ? __ldg(num_tiles_hit + i) : 0;
+    int x0 = 0, w = 1, y0 = 0, area = 0;
+    const bool windowed = FUSED && (wy0 > 0 || wy1 < TY);
+    if (windowed && cnt > 0) {              // row-sharded render: only the tile rows [wy0, wy1) of this rank count
+        gaussian_bbox(xys, radii, i, TX, TY, x0, w, y0, area, wy0, wy1);
+        cnt = area;
+    }
     int block_total;
     const int incl = block_incl_scan<SCAN_T>(cnt, s_warp, &block_total);
     if (tid < 32) {
@@ -205,8 +214,7 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
         }
     }
     if (FUSED && !(dbg & 1)) {
-        int x0 = 0, w = 1, y0 = 0, area = 0;
-        if (i < N && cnt > 0) gaussian_bbox(xys, radii, i, TX, TY, x0, w, y0, area);
+        if (!windowed && i < N && cnt > 0) gaussian_bbox(xys, radii, i, TX, TY, x0, w, y0, area);
         warp_emit<0>(cnt, block_excl + incl - cnt, x0, w, y0, area, i, 0, TX, capacity, keys_out, vals_out, s_hist, plan);
         __syncthreads();
         if (!(dbg & 2))
@@ -544,7 +552,7 @@ int gi2d_scan_tiles(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *to
     const int grid = (N + 1023) / 1024;
     const int ticket = all_resident(scan_kernel<false, 1024>, 1024, grid) ? 0 : 1;
     scan_kernel<false, 1024><<<grid, 1024, 0, stream>>>(N, num_tiles_hit, cum_tiles_hit, ctl, state, nullptr, nullptr, 0, 0, 0, nullptr,
-                                                   nullptr, none, nullptr, 0, nullptr, ticket, 0);
+                                                   nullptr, none, nullptr, 0, nullptr, ticket, 0, 0, 0x7fffffff);
     if (total_out) cudaMemcpyAsync(total_out, ctl + CTL_N, sizeof(int), cudaMemcpyDefault, stream);
     return cuda_status();
 }
@@ -625,18 +633,19 @@ size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity) {
     return fused_layout(N, TX * TY, capacity).total;
 }
 
-// scan + emit + sort + bin edges + record packing with the intersection count left on the device:
+// scan + emit + sort + bin edges + record packing with the intersection count left on the device, restricted to the
+// tile rows [ty_begin, ty_end) (a row-sharded render bins only its own rows; tile ids stay global):
 //   memset(control) -> scan_kernel<FUSED> -> onesweep pass(es) -> last onesweep pass (+ bin edges + packed records)
 //   status_out[0] = n_isect (may exceed capacity), status_out[1] = 1 when n_isect > capacity (results truncated).
 //   gids_sorted (capacity,) int32, packed (capacity*3) float4,
 //   tile_bins (TX*TY,2) int32: [lo,hi) per tile; EMPTY tiles hold (INT_MAX, 0) until gi2d_raster_sum_fwd_packed
 //   rewrites them to the reference's (0, 0).
 // Precondition (2D path): depths are all zero, so the key is the tile id alone.
-int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, const int *num_tiles_hit,
-                   const float *conics, const float *colors, const float *opacities, int capacity, void *ws,
-                   size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed, int *status_out,
-                   cudaStream_t stream) {
-    if (N <= 0 || TX <= 0 || TY <= 0 || capacity <= 0) return GI2D_ERR_INVALID;
+int gi2d_bin_fused_rows(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
+                        const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
+                        int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
+                        int *status_out, cudaStream_t stream) {
+    if (N <= 0 || TX <= 0 || TY <= 0 || capacity <= 0 || ty_begin < 0 || ty_end > TY || ty_begin >= ty_end) return GI2D_ERR_INVALID;
     const int T = TX * TY;
     const FusedLayout L = fused_layout(N, T, capacity);
     if (ws_bytes < L.total) return GI2D_ERR_WORKSPACE;
@@ -660,7 +669,8 @@ int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, co
         const int grid = (N + NT - 1) / NT;                                                                                \
         const int ticket = all_resident(scan_kernel<true, NT>, NT, grid) ? 0 : 1;                                          \
         scan_kernel<true, NT><<<grid, NT, 0, stream>>>(N, num_tiles_hit, nullptr, ctl, scan_state, xys, radii, TX, TY,     \
-                                                       capacity, k0, v0, plan, bins2, T, status_out, ticket, env_int("GI2D_DBG", 0)); \
+                                                       capacity, k0, v0, plan, bins2, T, status_out, ticket, env_int("GI2D_DBG", 0),  \
+                                                       ty_begin, ty_end);                                                 \
     }
     if (tn.scan_t == 256) GI2D_SCAN(256) else if (tn.scan_t == 512) GI2D_SCAN(512) else GI2D_SCAN(1024)
 #undef GI2D_SCAN
@@ -693,6 +703,15 @@ int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, co
         src_v = dst_v;
     }
     return cuda_status();
+}
+
+int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, const int *num_tiles_hit,
+                   const float *conics, const float *colors, const float *opacities, int capacity, void *ws,
+                   size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed, int *status_out,
+                   cudaStream_t stream) {
+    if (TY <= 0) return GI2D_ERR_INVALID;
+    return gi2d_bin_fused_rows(N, TX, TY, 0, TY, xys, radii, num_tiles_hit, conics, colors, opacities, capacity, ws, ws_bytes,
+                               gids_sorted, tile_bins, packed, status_out, stream);
 }
 
 }  // extern "C"

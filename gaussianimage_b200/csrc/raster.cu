@@ -78,7 +78,7 @@ __device__ __forceinline__ bool record_rect(const float4 &A, const float4 &B, in
 }
 
 template <bool TMA, bool AUX>
-__global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, int *tile_bins,
+__global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int *tile_bins,
                                                         const float4 *__restrict__ packed, GatherSrc src,
                                                         const int *__restrict__ d_status,
                                                         const float *__restrict__ background, float *__restrict__ out_img,
@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
     __shared__ uint8_t s_list[RB / 32][RB];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
+    const int tile = tile_begin + blockIdx.x;
     const int ty = tile / TX, tx = tile - ty * TX;
     const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
     // warp -> 8x4 pixel block (2 across, 4 down); lane -> pixel inside it
@@ -336,25 +336,33 @@ int gi2d_raster_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, co
     if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0) return GI2D_ERR_INVALID;
     GatherSrc src{gids_sorted, xys, conics, colors, opacities};
     if (final_Ts && final_idx)
-        raster_fwd_kernel<false, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx);
+        raster_fwd_kernel<false, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, 0, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx);
     else
-        raster_fwd_kernel<false, false><<<TX * TY, RB, 0, stream>>>(TX, W, H, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, nullptr, nullptr);
+        raster_fwd_kernel<false, false><<<TX * TY, RB, 0, stream>>>(TX, W, H, 0, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, nullptr, nullptr);
     return cuda_status();
 }
 
 // Forward over the packed records of gi2d_bin_fused (bulk-TMA staging).  d_status[0] == 0 (no intersections
 // anywhere) makes the kernel write `background` instead, as rasterize_sum.py:121-129 does.
+int gi2d_raster_sum_fwd_packed_rows(int TX, int TY, int W, int H, int ty_begin, int ty_end, int *tile_bins,
+                                    const float *packed, const int *d_status, const float *background, float *out_img,
+                                    float *final_Ts, int *final_idx, cudaStream_t stream) {
+    if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0 || ty_begin < 0 || ty_end > TY || ty_begin >= ty_end) return GI2D_ERR_INVALID;
+    GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
+    const float4 *p = reinterpret_cast<const float4 *>(packed);
+    const int grid = (ty_end - ty_begin) * TX, first = ty_begin * TX;
+    if (final_Ts && final_idx)
+        raster_fwd_kernel<true, true><<<grid, RB, 0, stream>>>(TX, W, H, first, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx);
+    else
+        raster_fwd_kernel<true, false><<<grid, RB, 0, stream>>>(TX, W, H, first, tile_bins, p, src, d_status, background, out_img, nullptr, nullptr);
+    return cuda_status();
+}
+
 int gi2d_raster_sum_fwd_packed(int TX, int TY, int W, int H, int *tile_bins, const float *packed,
                                const int *d_status, const float *background, float *out_img, float *final_Ts,
                                int *final_idx, cudaStream_t stream) {
-    if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0) return GI2D_ERR_INVALID;
-    GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
-    const float4 *p = reinterpret_cast<const float4 *>(packed);
-    if (final_Ts && final_idx)
-        raster_fwd_kernel<true, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx);
-    else
-        raster_fwd_kernel<true, false><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, p, src, d_status, background, out_img, nullptr, nullptr);
-    return cuda_status();
+    return gi2d_raster_sum_fwd_packed_rows(TX, TY, W, H, 0, TY, tile_bins, packed, d_status, background, out_img, final_Ts,
+                                           final_idx, stream);
 }
 
 // rasterize_sum_backward (reference ext.cpp:23 / bindings.cu:706-779).  The four outputs are zeroed here.

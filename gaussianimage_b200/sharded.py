@@ -1,0 +1,108 @@
+"""Multi-GPU forms of the path (new functionality; the reference is single-GPU, SURVEY.md sections 2.3 / 8e).
+
+* Image-parallel fitting (BASELINE config 4): every image is an independent optimisation, so ranks simply take images
+  `rank, rank + world, ...` -- `image_shard()`.  No collective touches the hot path.
+* Tile-row-sharded render-only decode of very large frames (BASELINE config 5): every rank holds all Gaussians,
+  projects them, bins and rasterizes ONLY the tile rows it owns (csrc: gi2d_bin_fused_rows /
+  gi2d_raster_sum_fwd_packed_rows) straight into its band of a full-size image buffer, and ONE in-place NCCL
+  all-gather over NVLink completes the frame on every rank -- `RowShardedRenderer`.  Bands are equal
+  (ceil(TY / world) tile rows, the buffer is padded to world * band rows) so that the all-gather needs no staging
+  and no reassembly.  Per-tile order and per-pixel arithmetic do not depend on which rank owns a tile, so the
+  gathered frame is bit-identical to the single-GPU one.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import cuda as _C
+from ._lib import check, lib
+
+
+def image_shard(num_images: int, rank: int, world: int) -> List[int]:
+    """Images fitted by `rank` (round-robin, like train.py:366-389's sequential loop dealt out to ranks)."""
+    return list(range(rank, num_images, world))
+
+
+def row_partition(tile_rows: int, world: int) -> List[Tuple[int, int]]:
+    """Equal bands of ceil(tile_rows / world) tile rows; trailing ranks may get a short or empty band."""
+    band = (tile_rows + world - 1) // world
+    return [(min(r * band, tile_rows), min((r + 1) * band, tile_rows)) for r in range(world)]
+
+
+class RowShardedRenderer:
+    """Render-only (decode) path sharded by tile rows over the ranks of `group` (None = single process)."""
+
+    def __init__(self, H: int, W: int, device, group: Optional[dist.ProcessGroup] = None, emulate_world: int = 0):
+        self.H, self.W = int(H), int(W)
+        self.TX, self.TY = (self.W + 15) // 16, (self.H + 15) // 16
+        self.group = group
+        self.world = dist.get_world_size(group) if (group is not None or dist.is_initialized()) else 1
+        self.rank = dist.get_rank(group) if self.world > 1 else 0
+        if emulate_world:           # tests: one process plays every rank in turn (set .rank, call render_band), no collective
+            self.world, self.rank = emulate_world, 0
+        self.bands = row_partition(self.TY, self.world)
+        self.band_rows = (self.TY + self.world - 1) // self.world * 16          # pixel rows per (padded) band
+        self.device = torch.device(device)
+        # full frame padded to world equal bands; frame() is the (H,W,3) view the caller sees
+        self.buffer = torch.zeros((self.world * self.band_rows, self.W, 3), dtype=torch.float32, device=self.device)
+        self.background = torch.ones(3, dtype=torch.float32, device=self.device)
+        self._cap = None
+        self.status = None
+
+    def frame(self) -> torch.Tensor:
+        return self.buffer[: self.H]
+
+    def render_band(self, xys, radii, conics, num_tiles_hit, colors, opacity) -> None:
+        """Bin + rasterize this rank's tile rows into its band of the frame buffer (asynchronous, current stream)."""
+        r0, r1 = self.bands[self.rank]
+        if r0 >= r1:
+            return
+        L, dev = lib(), self.device
+        N = xys.size(0)
+        if self._cap is None:
+            self._cap = max(int(4 * N * (r1 - r0) / max(self.TY, 1)) + (1 << 14), 1 << 14)
+        with torch.cuda.device(dev):
+            stream = _C._stream(dev)
+            while True:
+                cap = self._cap
+                ws_bytes = L.gi2d_bin_fused_workspace_bytes(N, self.TX, self.TY, cap)
+                if getattr(self, "_ws_cap", None) != cap:       # persistent workspace (decode loops reuse it)
+                    self._ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+                    self._gids = torch.empty((cap,), dtype=torch.int32, device=dev)
+                    self._bins = torch.empty((self.TX * self.TY, 2), dtype=torch.int32, device=dev)
+                    self._packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
+                    self.status = torch.zeros((2,), dtype=torch.int32, device=dev)
+                    self._ws_cap = cap
+                check(L.gi2d_bin_fused_rows(N, self.TX, self.TY, r0, r1, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(),
+                                            conics.data_ptr(), colors.data_ptr(), opacity.data_ptr(), cap, self._ws.data_ptr(),
+                                            ws_bytes, self._gids.data_ptr(), self._bins.data_ptr(), self._packed.data_ptr(),
+                                            self.status.data_ptr(), stream), "bin_fused_rows")
+                # H here is the padded buffer height so that every pixel row of the band exists
+                check(L.gi2d_raster_sum_fwd_packed_rows(self.TX, self.TY, self.W, self.buffer.shape[0], r0, r1, self._bins.data_ptr(),
+                                                        self._packed.data_ptr(), 0, 0, self.buffer.data_ptr(), 0, 0, stream),
+                      "rasterize_sum_forward (rows)")
+                if torch.cuda.is_current_stream_capturing() or getattr(self, "_cap_checked", False):
+                    break
+                n, over = self.status.tolist()
+                if not over:
+                    self._cap_checked = True
+                    break
+                self._cap = int(n * 1.25) + 1024
+
+    def gather(self) -> torch.Tensor:
+        """In-place all-gather of the bands (every rank contributes buffer[rank*band : (rank+1)*band])."""
+        if self.world > 1 and dist.is_initialized():
+            mine = self.buffer[self.rank * self.band_rows: (self.rank + 1) * self.band_rows]
+            dist.all_gather_into_tensor(self.buffer, mine, group=self.group)
+        return self.frame()
+
+    def render(self, means2d, L_elements, colors, opacity) -> torch.Tensor:
+        """decode step: project all Gaussians (every rank), render own band, all-gather -> (H,W,3) frame."""
+        N = means2d.shape[0]
+        xys, depths, radii, conics, nth = _C.project_gaussians_2d_forward(N, means2d, L_elements, self.H, self.W,
+                                                                          (self.TX, self.TY, 1))
+        self.render_band(xys, radii, conics, nth, colors, opacity)
+        return self.gather()

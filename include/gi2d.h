@@ -120,6 +120,13 @@ int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, co
                    size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed, int *status_out,
                    cudaStream_t stream);
 
+/* Row-sharded variant (render-only decode of very large frames, one rank per band of tile rows): only intersections
+ * with tile rows [ty_begin, ty_end) are counted, emitted and sorted; tile ids and tile_bins stay global (TX*TY rows). */
+int gi2d_bin_fused_rows(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
+                        const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
+                        int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
+                        int *status_out, cudaStream_t stream);
+
 /* ---- accumulated-sum rasterizer --------------------------------------------------------------------------------- */
 
 /* Replaces rasterize_sum_forward (ext.cpp:22 -> bindings.cu:400-469 -> forward.cu:512-627).
@@ -135,6 +142,11 @@ int gi2d_raster_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, co
 int gi2d_raster_sum_fwd_packed(int TX, int TY, int W, int H, int *tile_bins, const float *packed,
                                const int *d_status, const float *background, float *out_img, float *final_Ts,
                                int *final_idx, cudaStream_t stream);
+
+/* Row-sharded variant: rasterizes only the tiles of rows [ty_begin, ty_end) into the same full-size out_img. */
+int gi2d_raster_sum_fwd_packed_rows(int TX, int TY, int W, int H, int ty_begin, int ty_end, int *tile_bins,
+                                    const float *packed, const int *d_status, const float *background, float *out_img,
+                                    float *final_Ts, int *final_idx, cudaStream_t stream);
 
 /* Replaces rasterize_sum_backward (ext.cpp:23 -> bindings.cu:706-779 -> backward.cu:696-862).
  * v_out (H,W,3).  Outputs v_xy (N,2), v_conic (N,3), v_colors (N,3), v_opacity (N,1) are zeroed by the call.

@@ -1,0 +1,54 @@
+"""The C-ABI library loads without a GPU and exports exactly what include/gi2d.h declares (no compute calls here)."""
+import ctypes
+import re
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def declared():
+    text = (ROOT / "include" / "gi2d.h").read_text()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(gi2d_\w+)\s*\(", text)))
+
+
+def test_header_declares_the_hot_path_entry_points():
+    names = declared()
+    for must in ("gi2d_project_cholesky_fwd", "gi2d_project_cholesky_bwd", "gi2d_project_scale_rot_fwd", "gi2d_project_scale_rot_bwd",
+                 "gi2d_cov2d_bounds", "gi2d_scan_tiles", "gi2d_emit_isects", "gi2d_sort_isects", "gi2d_tile_bins", "gi2d_bin_fused",
+                 "gi2d_raster_sum_fwd", "gi2d_raster_sum_bwd", "gi2d_raster_sum_fwd_packed", "gi2d_raster_sum_bwd_packed"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    from gaussianimage_b200 import _lib
+    lib = ctypes.CDLL(str(_lib.LIB_PATH))
+    missing = [n for n in declared() if not hasattr(lib, n)]
+    assert not missing, f"declared in include/gi2d.h but not exported by libgi2d.so: {missing}"
+    assert set(_lib.EXPORTS) == set(declared()), "gaussianimage_b200/_lib.py signatures out of sync with include/gi2d.h"
+    assert _lib.lib().gi2d_abi_version() == 1
+    assert _lib.lib().gi2d_status_string(0) == b"ok" and _lib.lib().gi2d_status_string(2) == b"workspace too small"
+
+
+def test_workspace_queries_are_host_only_and_monotone():
+    from gaussianimage_b200._lib import lib
+    L = lib()
+    a = L.gi2d_bin_fused_workspace_bytes(70000, 48, 32, 280000)
+    b = L.gi2d_bin_fused_workspace_bytes(70000, 48, 32, 560000)
+    assert 0 < a < b
+    assert L.gi2d_sort_workspace_bytes(1000, 32, 43) < L.gi2d_sort_workspace_bytes(1000, 0, 64)
+    assert L.gi2d_scan_workspace_bytes(70000) > 0
+
+
+def test_library_is_sm100a_with_tma_and_no_fallback():
+    import shutil
+    import subprocess
+    from gaussianimage_b200 import _lib
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not available")
+    out = subprocess.run(["cuobjdump", "-lelf", str(_lib.LIB_PATH)], capture_output=True, text=True).stdout
+    assert "sm_100a" in out and "sm_90" not in out
+    sass = subprocess.run(["cuobjdump", "-sass", str(_lib.LIB_PATH)], capture_output=True, text=True).stdout
+    assert "UBLKCP" in sass, "the rasterizers must stage their batches with bulk TMA copies"
