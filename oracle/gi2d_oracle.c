@@ -17,12 +17,15 @@
  * bit for bit; the only operations a CPU cannot reproduce bit-wise are MUFU.EX2 (`__expf`) and
  * libdevice sinf/cosf -- handled with the `ambig` outputs below.
  *
- * Parity pinning status: compute_cov2d_bounds / map_gaussian_to_intersects / get_tile_bin_edges
- * are pinned against the reference's own _torch_impl.py (tests/golden/, generated by
- * tests/golden/make_golden.py).  Projection, rasterize-sum forward/backward and projection
- * backward have NO CPU implementation and NO test in the reference; they are pinned on the GPU box
- * against the reference's own CUDA kernels compiled from /root/reference (oracle/_ref), and from
- * those runs golden vectors are committed under tests/golden/ (see DESIGN.md section 6).
+ * Parity pinning status: PINNED.  compute_cov2d_bounds / map_gaussian_to_intersects / get_tile_bin_edges
+ * against the reference's own _torch_impl.py (tests/golden/ref_torch_impl.npz, made by
+ * tests/golden/make_golden.py in the build container).  Projection (both parametrisations),
+ * rasterize-sum forward/backward and projection backward -- which the reference neither tests nor
+ * implements on the CPU -- against OUTPUTS OF THE REFERENCE'S OWN CUDA KERNELS, compiled in place from
+ * /root/reference (oracle/_ref) and run on a B200: tests/golden/ref_cuda_kernels.npz, made by
+ * tests/golden/make_golden_refcuda.py, checked by tests/test_oracle_vs_refcuda_golden_cpu.py
+ * (integers, tile lists, bin edges and Cholesky projection floats bit-exact; image 1e-5; gradients
+ * 1e-4).  See DESIGN.md section 6.
  */
 #include <math.h>
 #include <stdint.h>

@@ -18,7 +18,8 @@
  *   bindings.cu:400-469  rasterize_forward_sum_tensor               (grid tiles, block 16x16)
  *   bindings.cu:706-779  rasterize_backward_sum_tensor
  * All kernels go to the legacy default stream like the reference (quirk Q9); callers synchronise.
- * Outputs must be zero-filled by the caller (the reference uses torch::zeros).
+ * Outputs must be zero-filled by the caller (the reference uses torch::zeros).  `background_host` is a HOST pointer to
+ * 3 floats (the kernels take the colour by value; they never use it, quirk Q6).
  */
 #include "forward.cuh"
 #include "backward.cuh"
@@ -89,23 +90,23 @@ REF_API int ref_get_tile_bin_edges(int n, const long long *isect_ids_sorted, int
 
 REF_API int ref_rasterize_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, const int *tile_bins,
                                   const float *xys, const float *conics, const float *colors, const float *opac,
-                                  const float *background_dev, float *out_img, float *final_Ts, int *final_idx) {
+                                  const float *background_host, float *out_img, float *final_Ts, int *final_idx) {
     dim3 tb(TX, TY, 1), block(BLOCK_X, BLOCK_Y, 1), img(W, H, 1);
     rasterize_forward_sum<<<tb, block>>>(tb, img, gids_sorted, (const int2 *)tile_bins, (const float2 *)xys,
                                          (const float3 *)conics, (const float3 *)colors, opac, final_Ts, final_idx,
-                                         (float3 *)out_img, *(const float3 *)background_dev);
+                                         (float3 *)out_img, *(const float3 *)background_host);
     return last_err();
 }
 
 REF_API int ref_rasterize_sum_bwd(int TX, int TY, int W, int H, const int *gids_sorted, const int *tile_bins,
                                   const float *xys, const float *conics, const float *colors, const float *opac,
-                                  const float *background_dev, const float *final_Ts, const int *final_idx,
+                                  const float *background_host, const float *final_Ts, const int *final_idx,
                                   const float *v_out, const float *v_out_alpha, float *v_xy, float *v_conic,
                                   float *v_colors, float *v_opacity) {
     dim3 tb(TX, TY, 1), block(BLOCK_X, BLOCK_Y, 1), img(W, H, 1);
     rasterize_backward_sum_kernel<<<tb, block>>>(
         tb, img, gids_sorted, (const int2 *)tile_bins, (const float2 *)xys, (const float3 *)conics,
-        (const float3 *)colors, opac, *(const float3 *)background_dev, final_Ts, final_idx, (const float3 *)v_out,
+        (const float3 *)colors, opac, *(const float3 *)background_host, final_Ts, final_idx, (const float3 *)v_out,
         v_out_alpha, (float2 *)v_xy, (float3 *)v_conic, (float3 *)v_colors, v_opacity);
     return last_err();
 }

@@ -99,7 +99,7 @@ def rasterize_sum_fwd(H, W, gids_s, bins, xys, conics, colors, opac, flavor="jit
     TX, TY = (W + 15) // 16, (H + 15) // 16
     out, Ts = torch.zeros(H, W, 3, device=dev), torch.zeros(H, W, device=dev)
     fidx = torch.zeros(H, W, dtype=torch.int32, device=dev)
-    bg = torch.ones(3, device=dev)
+    bg = torch.ones(3)                      # host: the harness passes it by value
     torch.cuda.synchronize()
     _ok(lib(flavor).ref_rasterize_sum_fwd(TX, TY, W, H, _p(gids_s), _p(bins), _p(xys), _p(conics), _p(colors), _p(opac), _p(bg),
                                           _p(out), _p(Ts), _p(fidx)), "rasterize_sum_fwd")
@@ -111,7 +111,7 @@ def rasterize_sum_bwd(H, W, gids_s, bins, xys, conics, colors, opac, Ts, fidx, v
     TX, TY = (W + 15) // 16, (H + 15) // 16
     v_xy, v_conic = torch.zeros(N, 2, device=dev), torch.zeros(N, 3, device=dev)
     v_col, v_op = torch.zeros(N, 3, device=dev), torch.zeros(N, 1, device=dev)
-    bg, v_alpha = torch.ones(3, device=dev), torch.zeros(H, W, device=dev)
+    bg, v_alpha = torch.ones(3), torch.zeros(H, W, device=dev)
     torch.cuda.synchronize()
     _ok(lib(flavor).ref_rasterize_sum_bwd(TX, TY, W, H, _p(gids_s), _p(bins), _p(xys), _p(conics), _p(colors), _p(opac), _p(bg),
                                           _p(Ts), _p(fidx), _p(v_out), _p(v_alpha), _p(v_xy), _p(v_conic), _p(v_col), _p(v_op)),
