@@ -158,12 +158,23 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
     }
 }
 
-// Backward.  Work unit = one ALIGNED GROUP OF 4 PIXELS of one row of one staged record's visible rectangle.  The
-// 256 threads of the CTA walk the flattened list of units of all records of the tile, 256 units per round, so every
-// lane always has exactly four (masked) pixel evaluations to do, whatever the records' footprints are.  A unit's 9
-// partial gradients go to shared memory with plain stores; the thread that owns a record then adds up the partials
-// of that record's units of the round in registers.  No shuffle reductions, no shared-memory atomics; per
-// (tile, Gaussian) one set of global reductions -- three 16-byte vector `red.global.add.v4.f32` in the packed layout.
+// Backward.  Work unit = one ALIGNED GROUP OF 4 PIXELS of one row of one staged record's visible rectangle.  The units
+// of all records of the tile form one flattened list (record-major, row-major inside a record); thread t owns the
+// CONTIGUOUS chunk [t*R, t*R+R) of it (R = ceil(units/256)), so every lane has the same number of four-pixel
+// evaluations whatever the records' footprints are, and a thread's consecutive units mostly belong to one record:
+// its partial sums stay in registers and are flushed only when the chunk crosses into the next record -- with nine
+// PLAIN shared-memory stores into slot (thread + record): along the flattened list the (thread, record) pairs form a
+// monotone staircase, so that sum is unique per flush (shared-memory float atomics are CAS loops on sm_100).  No
+// barrier inside the main loop, no shuffle reductions, no shared atomics; after one final barrier the thread that
+// staged record t adds up the slots of the threads [pref[t]/R, (pref[t+1]-1)/R] whose chunks intersect it, turns the
+// sums into the nine gradients and issues ONE set of global reductions per (tile, Gaussian): three 16-byte
+// `red.global.add.v4.f32` in the packed layout.
+//
+// Sums kept per record (m = vis * v_alpha for a contributing pixel, 0 otherwise; dx, dy as in backward.cu:797-799):
+//   S_m = sum m, S_x = sum m dx, S_y = sum m dy, S_xx = sum m dx dx, S_xy = sum m dx dy, S_yy = sum m dy dy, and
+//   sum alpha * v_out per channel.  With v_sigma = -opac * m (backward.cu:822) the reference's per-pixel terms
+//   (:823-828) factor into  v_conic = -0.5 opac (S_xx, S_xy, S_yy),  v_xy = -opac (cx S_x + cy S_y, cy S_x + cz S_y),
+//   v_opacity = S_m  -- the same fp32 sums re-associated, well inside the 1e-4 gradient tolerance.
 __device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -179,10 +190,9 @@ __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, co
                                                         const float *__restrict__ v_out, GradOut out) {
     __shared__ __align__(128) float4 s_rec[RB * 3];
     __shared__ __align__(16) float s_v[3][GI2D_TILE_PIX];      // upstream gradient, one plane per channel
-    __shared__ float s_part[9][RB];                            // per-unit partials of the current round
+    __shared__ float s_part[9][2 * RB];                        // flushed partial sums, slot = thread + record
     __shared__ uint32_t s_rect[RB];                            // x0 | x1<<4 | y0<<8 | g0<<12 | segs<<14 | rows<<17
-    __shared__ uint16_t s_pref[RB];                            // exclusive prefix of the unit counts
-    __shared__ uint8_t s_owner[RB];                            // unit of the current round -> record
+    __shared__ uint16_t s_pref[RB + 1];                        // exclusive prefix of the unit counts; [RB] = total
     __shared__ int s_warp[RB / 32];
     __shared__ __align__(8) uint64_t s_bar;
 
@@ -234,92 +244,135 @@ __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, co
         wbase += (w < warp) ? c : 0;
         total += c;
     }
-    const int ubeg = wbase + incl - units, uend = ubeg + units;     // this record's units in the flattened list
-    s_pref[tid] = (uint16_t)ubeg;
+    s_pref[tid] = (uint16_t)(wbase + incl - units);
+    if (tid == 0) s_pref[RB] = (uint16_t)total;
+    __syncthreads();
+    if (total == 0) return;
 
-    float acc[9];
+    // ---- main loop: this thread's contiguous chunk of the flattened unit list
+    const int R = (total + RB - 1) / RB;
+    int u = tid * R;
+    const int uend = min(total, u + R);
+    if (u < uend) {
+        // record containing unit u: the largest t with s_pref[t] <= u (records without units share their successor's prefix)
+        int t = 0;
 #pragma unroll
-    for (int c = 0; c < 9; ++c) acc[c] = 0.f;
-
-    for (int base = 0; base < total; base += RB) {
-        // (a) owners of this round's units
-        for (int u = max(ubeg, base); u < min(uend, base + RB); ++u) s_owner[u - base] = (uint8_t)tid;
-        __syncthreads();
-        // (b) one unit per thread: four masked pixel evaluations
-        if (base + tid < total) {
-            const int t = s_owner[tid];
-            const uint32_t rect = s_rect[t];
-            const int x0 = rect & 15, x1 = (rect >> 4) & 15, y0 = (rect >> 8) & 15, g0 = (rect >> 12) & 3, segs = (rect >> 14) & 7;
-            const int k = base + tid - (int)s_pref[t];
-            const int row = segs == 1 ? k : segs == 2 ? (k >> 1) : segs == 4 ? (k >> 2) : ((k * 43) >> 7);
-            const int g = g0 + (k - row * segs);
-            const int ly = y0 + row;
+        for (int step = RB / 2; step > 0; step >>= 1)
+            if ((int)s_pref[t + step] <= u) t += step;
+        float S_m = 0.f, S_x = 0.f, S_y = 0.f, S_xx = 0.f, S_xy = 0.f, S_yy = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f;
+        // current record (registers) and position (row, seg) inside its rectangle
+        float x, y, opac, cx, cy, cz, cr, cg, cb;
+        int x0, x1, y0, g0, segs, rec_end, row, seg;
+        auto load_record = [&]() {
             const float4 A = s_rec[3 * t], B = s_rec[3 * t + 1];
-            const float cb = s_rec[3 * t + 2].x;
-            const float x = A.x, opac = A.z, cx = A.w, cy = B.x, cz = B.y, cr = B.z, cg = B.w;
-            const float dy = fsub(A.y, (float)(ty0 + ly));
+            cb = s_rec[3 * t + 2].x;
+            x = A.x; y = A.y; opac = A.z; cx = A.w; cy = B.x; cz = B.y; cr = B.z; cg = B.w;
+            const uint32_t rect = s_rect[t];
+            x0 = rect & 15; x1 = (rect >> 4) & 15; y0 = (rect >> 8) & 15; g0 = (rect >> 12) & 3; segs = (rect >> 14) & 7;
+            rec_end = (int)s_pref[t + 1];
+            const int k = u - (int)s_pref[t];
+            row = segs == 1 ? k : segs == 2 ? (k >> 1) : segs == 4 ? (k >> 2) : ((k * 43) >> 7);
+            seg = k - row * segs;
+        };
+        auto flush = [&]() {
+            const int slot = tid + t;
+            s_part[0][slot] = S_x; s_part[1][slot] = S_y; s_part[2][slot] = S_xx; s_part[3][slot] = S_xy; s_part[4][slot] = S_yy;
+            s_part[5][slot] = a_r; s_part[6][slot] = a_g; s_part[7][slot] = a_b; s_part[8][slot] = S_m;
+        };
+        load_record();
+        // ONE flat loop over the chunk: crossing into the next record is a short divergent branch, the four-pixel body
+        // stays converged across the warp (an inner per-record loop would make lanes wait for each other's records)
+        for (; u < uend; ++u) {
+            if (u >= rec_end) {
+                flush();
+                S_m = S_x = S_y = S_xx = S_xy = S_yy = a_r = a_g = a_b = 0.f;
+                do { ++t; } while ((int)s_pref[t + 1] <= u);        // next record that has units
+                load_record();
+            }
+            const int ly = y0 + row, g = g0 + seg;
+            const float dy = fsub(y, (float)(ty0 + ly));
             const float t3 = fmul(dy, fmul(cz, dy));
-            const float cydy = cy * dy, czdy = cz * dy;
             const float4 vr4 = reinterpret_cast<const float4 *>(s_v[0])[ly * 4 + g];
             const float4 vg4 = reinterpret_cast<const float4 *>(s_v[1])[ly * 4 + g];
             const float4 vb4 = reinterpret_cast<const float4 *>(s_v[2])[ly * 4 + g];
             const float vr[4] = {vr4.x, vr4.y, vr4.z, vr4.w}, vg[4] = {vg4.x, vg4.y, vg4.z, vg4.w}, vb[4] = {vb4.x, vb4.y, vb4.z, vb4.w};
-            float a_r = 0.f, a_g = 0.f, a_b = 0.f, a_cxx = 0.f, a_cxy = 0.f, a_cyy = 0.f, a_x = 0.f, a_y = 0.f, a_o = 0.f;
             const float fx0 = (float)(tx0 + 4 * g);
+            float u_m = 0.f, u_x = 0.f;              // this unit's sum m and sum m dx (dy is constant over the unit)
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int lx = 4 * g + j;
                 const float dx = fsub(x, fx0 + (float)j);
                 const float q = ffma(dx, fmul(cx, dx), t3);
                 const float sigma = ffma(dy, fmul(cy, dx), fmul(q, 0.5f));
-                float vis = exp_neg(sigma);
+                const float vis = exp_neg(sigma);
                 const float raw = fminf(fmul(opac, vis), 1.f);
                 const bool valid = lx >= x0 && lx <= x1 && !(sigma < 0.f) && !(raw < GI2D_ALPHA_MIN);   // backward.cu:806-808
                 const float alpha = valid ? raw : 0.f;
-                vis = valid ? vis : 0.f;
                 a_r = fmaf(alpha, vr[j], a_r); a_g = fmaf(alpha, vg[j], a_g); a_b = fmaf(alpha, vb[j], a_b);   // backward.cu:814
                 const float v_alpha = fmaf(cr, vr[j], fmaf(cg, vg[j], cb * vb[j]));                          // :818-820
-                const float v_sigma = -(opac * vis) * v_alpha;                                               // :822
-                const float hs = 0.5f * v_sigma;
-                const float hdx = hs * dx;
-                a_cxx = fmaf(hdx, dx, a_cxx); a_cxy = fmaf(hdx, dy, a_cxy); a_cyy = fmaf(hs * dy, dy, a_cyy);   // :823-825
-                a_x = fmaf(v_sigma, fmaf(cx, dx, cydy), a_x);                                                // :826-827
-                a_y = fmaf(v_sigma, fmaf(cy, dx, czdy), a_y);
-                a_o = fmaf(vis, v_alpha, a_o);                                                               // :828
+                const float m = valid ? vis * v_alpha : 0.f;
+                const float mdx = m * dx;
+                u_m += m;
+                u_x += mdx;
+                S_xx = fmaf(mdx, dx, S_xx);
             }
-            s_part[0][tid] = a_x; s_part[1][tid] = a_y; s_part[2][tid] = a_cxx; s_part[3][tid] = a_cxy; s_part[4][tid] = a_cyy;
-            s_part[5][tid] = a_r; s_part[6][tid] = a_g; s_part[7][tid] = a_b; s_part[8][tid] = a_o;
+            S_m += u_m; S_x += u_x;
+            const float mdy = u_m * dy;
+            S_y += mdy;
+            S_yy = fmaf(mdy, dy, S_yy);
+            S_xy = fmaf(u_x, dy, S_xy);
+            if (++seg == segs) { seg = 0; ++row; }
         }
-        __syncthreads();
-        // (c) every record adds up its units of this round
-        for (int u = max(ubeg, base) - base; u < min(uend, base + RB) - base; ++u) {
-#pragma unroll
-            for (int c = 0; c < 9; ++c) acc[c] += s_part[c][u];
-        }
-        // the next round's (a) writes s_owner only; its barrier also orders these reads before the next (b)
+        flush();
     }
-    if (units == 0) return;
-    bool any = false;
-#pragma unroll
-    for (int c = 0; c < 9; ++c) any |= acc[c] != 0.f;
-    if (!any) return;
+    __syncthreads();
+    if (tid >= cnt || units == 0) return;
+    float S_x = 0.f, S_y = 0.f, S_xx = 0.f, S_xy = 0.f, S_yy = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f, S_m = 0.f;
+    {
+        const int ubeg = (int)s_pref[tid];
+        const int ta = ubeg / R, tb = (ubeg + units - 1) / R;           // threads whose chunks intersect this record
+        for (int slot = ta + tid; slot <= tb + tid; ++slot) {
+            S_x += s_part[0][slot]; S_y += s_part[1][slot]; S_xx += s_part[2][slot]; S_xy += s_part[3][slot]; S_yy += s_part[4][slot];
+            a_r += s_part[5][slot]; a_g += s_part[6][slot]; a_b += s_part[7][slot]; S_m += s_part[8][slot];
+        }
+    }
+    if (S_x == 0.f && S_y == 0.f && S_xx == 0.f && S_xy == 0.f && S_yy == 0.f && a_r == 0.f && a_g == 0.f && a_b == 0.f && S_m == 0.f)
+        return;
+    const float4 A = s_rec[3 * tid], B = s_rec[3 * tid + 1];
+    const float nop = -A.z, hop = -0.5f * A.z;                 // v_sigma = -opac * m ; the conic terms carry 0.5 (Q7)
+    const float g_x = nop * fmaf(A.w, S_x, B.x * S_y), g_y = nop * fmaf(B.x, S_x, B.y * S_y);   // backward.cu:826-827
+    const float g_cxx = hop * S_xx, g_cxy = hop * S_xy, g_cyy = hop * S_yy;                    // :823-825
     const size_t gid = (size_t)__float_as_int(s_rec[3 * tid + 2].y);
     if (VEC12) {
         float *row = out.g12 + 12 * gid;
-        red_add_v4(row, acc[0], acc[1], acc[2], acc[3]);
-        red_add_v4(row + 4, acc[4], acc[5], acc[6], acc[7]);
-        atomicAdd(row + 8, acc[8]);
+        red_add_v4(row, g_x, g_y, g_cxx, g_cxy);
+        red_add_v4(row + 4, g_cyy, a_r, a_g, a_b);
+        atomicAdd(row + 8, S_m);
     } else {
-        atomicAdd(out.v_xy + 2 * gid, acc[0]); atomicAdd(out.v_xy + 2 * gid + 1, acc[1]);
-        atomicAdd(out.v_conic + 3 * gid, acc[2]); atomicAdd(out.v_conic + 3 * gid + 1, acc[3]); atomicAdd(out.v_conic + 3 * gid + 2, acc[4]);
-        atomicAdd(out.v_colors + 3 * gid, acc[5]); atomicAdd(out.v_colors + 3 * gid + 1, acc[6]); atomicAdd(out.v_colors + 3 * gid + 2, acc[7]);
-        atomicAdd(out.v_opacity + gid, acc[8]);
+        atomicAdd(out.v_xy + 2 * gid, g_x); atomicAdd(out.v_xy + 2 * gid + 1, g_y);
+        atomicAdd(out.v_conic + 3 * gid, g_cxx); atomicAdd(out.v_conic + 3 * gid + 1, g_cxy); atomicAdd(out.v_conic + 3 * gid + 2, g_cyy);
+        atomicAdd(out.v_colors + 3 * gid, a_r); atomicAdd(out.v_colors + 3 * gid + 1, a_g); atomicAdd(out.v_colors + 3 * gid + 2, a_b);
+        atomicAdd(out.v_opacity + gid, S_m);
     }
 }
 
 static inline int cuda_status() {
     const cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
+}
+
+// The rasterizers are limited to 4 CTAs/SM by registers; ask for the shared-memory carve-out that lets 4 of them fit.
+template <typename K>
+static void prefer_shared(K kernel) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+static void init_once() {
+    static bool done = false;
+    if (done) return;
+    done = true;
+    prefer_shared(raster_bwd_kernel<true, true>);
+    prefer_shared(raster_bwd_kernel<false, false>);
+    cudaGetLastError();
 }
 
 }  // namespace gi2d
@@ -373,6 +426,7 @@ int gi2d_raster_sum_bwd(int N, int TX, int TY, int W, int H, const int *gids_sor
                         float *v_opacity, cudaStream_t stream) {
     (void)final_idx;
     if (N <= 0 || TX <= 0 || TY <= 0) return GI2D_ERR_INVALID;
+    init_once();
     cudaMemsetAsync(v_xy, 0, sizeof(float) * 2 * (size_t)N, stream);
     cudaMemsetAsync(v_conic, 0, sizeof(float) * 3 * (size_t)N, stream);
     cudaMemsetAsync(v_colors, 0, sizeof(float) * 3 * (size_t)N, stream);
@@ -390,6 +444,7 @@ int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *t
                                const float *v_out, float *grads12, cudaStream_t stream) {
     if (N <= 0 || TX <= 0 || TY <= 0) return GI2D_ERR_INVALID;
     if (reinterpret_cast<uintptr_t>(grads12) & 15) return GI2D_ERR_INVALID;
+    init_once();
     cudaMemsetAsync(grads12, 0, sizeof(float) * 12 * (size_t)N, stream);
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     GradOut out{grads12, nullptr, nullptr, nullptr, nullptr};
