@@ -37,8 +37,29 @@ def _i32(x: Tensor, name: str) -> Tensor:
     return x
 
 
+class _NoGuard:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NOGUARD = _NoGuard()
+
+
+def _guard(device):
+    """Device guard that costs nothing when `device` is already current (the usual case; torch.cuda.device() costs
+    several microseconds per use, which matters on a path whose whole forward is ~60 us of GPU time)."""
+    if device.index is None or device.index == torch._C._cuda_getDevice():
+        return _NOGUARD
+    return torch.cuda.device(device)
+
+
 def _stream(device) -> int:
-    return torch.cuda.current_stream(device).cuda_stream
+    """Raw cudaStream_t of torch's current stream on `device` (the reference uses the legacy default stream, Q9)."""
+    idx = device.index
+    return torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice() if idx is None else idx)
 
 
 def _p(x) -> int:
@@ -50,7 +71,7 @@ def project_gaussians_2d_forward(num_points: int, means2d: Tensor, L_elements: T
     """ext.cpp:16 -> bindings.cu:781-839. Returns (xys, depths, radii, conics, num_tiles_hit)."""
     means2d, L = _f32(means2d, "means2d"), _f32(L_elements, "L_elements")
     N, dev = int(num_points), means2d.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         xys = torch.empty((N, 2), dtype=torch.float32, device=dev)
         depths = torch.empty((N,), dtype=torch.float32, device=dev)
         radii = torch.empty((N,), dtype=torch.int32, device=dev)
@@ -68,7 +89,7 @@ def project_gaussians_2d_scale_rot_forward(num_points: int, means2d: Tensor, sca
     """ext.cpp:18 -> bindings.cu:841-899."""
     means2d, scales2d, rotation = _f32(means2d, "means2d"), _f32(scales2d, "scales2d"), _f32(rotation, "rotation")
     N, dev = int(num_points), means2d.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         xys = torch.empty((N, 2), dtype=torch.float32, device=dev)
         depths = torch.empty((N,), dtype=torch.float32, device=dev)
         radii = torch.empty((N,), dtype=torch.int32, device=dev)
@@ -88,7 +109,7 @@ def project_gaussians_2d_backward(num_points: int, means2d: Tensor, L_elements: 
     L, radii, conics = _f32(L_elements, "L_elements"), _i32(radii, "radii"), _f32(conics, "conics")
     v_xy, v_conic = _f32(v_xy.contiguous(), "v_xy"), _f32(v_conic.contiguous(), "v_conic")
     N, dev = int(num_points), L.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         v_cov2d = torch.empty((N, 3), dtype=torch.float32, device=dev) if want_cov2d else None
         v_mean2d = torch.empty((N, 2), dtype=torch.float32, device=dev)
         v_L = torch.empty((N, 3), dtype=torch.float32, device=dev)
@@ -106,7 +127,7 @@ def project_gaussians_2d_scale_rot_backward(num_points: int, means2d: Tensor, sc
     radii, conics = _i32(radii, "radii"), _f32(conics, "conics")
     v_xy, v_conic = _f32(v_xy.contiguous(), "v_xy"), _f32(v_conic.contiguous(), "v_conic")
     N, dev = int(num_points), scales2d.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         v_cov2d = torch.empty((N, 3), dtype=torch.float32, device=dev) if want_cov2d else None
         v_mean2d = torch.empty((N, 2), dtype=torch.float32, device=dev)
         v_scale = torch.empty((N, 2), dtype=torch.float32, device=dev)
@@ -122,7 +143,7 @@ def compute_cov2d_bounds(num_pts: int, cov2d: Tensor):
     """ext.cpp:12 -> bindings.cu:41-61. Returns (conics (N,3), radii (N,1) float32)."""
     cov2d = _f32(cov2d, "cov2d")
     N, dev = int(num_pts), cov2d.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         conics = torch.empty((N, 3), dtype=torch.float32, device=dev)
         radii = torch.empty((N, 1), dtype=torch.float32, device=dev)
         check(lib().gi2d_cov2d_bounds(N, _p(cov2d), _p(conics), _p(radii), _stream(dev)), "compute_cov2d_bounds")
@@ -135,7 +156,7 @@ def map_gaussian_to_intersects(num_points: int, num_intersects: int, xys: Tensor
     xys, depths = _f32(xys, "xys"), _f32(depths, "depths")
     radii, cum = _i32(radii, "radii"), _i32(cum_tiles_hit, "cum_tiles_hit")
     dev = xys.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         ids = torch.empty((num_intersects,), dtype=torch.int64, device=dev)
         gids = torch.empty((num_intersects,), dtype=torch.int32, device=dev)
         check(lib().gi2d_emit_isects(int(num_points), _p(xys), _p(depths), _p(radii), _p(cum), tile_bounds[0], tile_bounds[1],
@@ -150,7 +171,7 @@ def get_tile_bin_edges(num_intersects: int, isect_ids_sorted: Tensor, n_bins: in
         raise RuntimeError("isect_ids_sorted must be int64")
     dev = isect_ids_sorted.device
     rows = int(num_intersects) if n_bins is None else int(n_bins)
-    with torch.cuda.device(dev):
+    with _guard(dev):
         bins = torch.empty((rows, 2), dtype=torch.int32, device=dev)
         check(lib().gi2d_tile_bins(int(num_intersects), _p(isect_ids_sorted), rows, _p(bins), _stream(dev)), "get_tile_bin_edges")
     return bins
@@ -160,7 +181,7 @@ def sort_isects(isect_ids: Tensor, gaussian_ids: Tensor, begin_bit: int = 0, end
     """torch.sort + torch.gather of utils.py:164-165 as one stable onesweep radix sort."""
     _chk(isect_ids, "isect_ids"); _i32(gaussian_ids, "gaussian_ids")
     n, dev = isect_ids.numel(), isect_ids.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         ids_s, gids_s = torch.empty_like(isect_ids), torch.empty_like(gaussian_ids)
         if n:
             nbytes = lib().gi2d_sort_workspace_bytes(n, begin_bit, end_bit)
@@ -174,7 +195,7 @@ def scan_tiles(num_tiles_hit: Tensor):
     """torch.cumsum(int32) of utils.py:116 -> (cum (N,) int32, total (1,) int32 device tensor)."""
     nth = _i32(num_tiles_hit, "num_tiles_hit")
     N, dev = nth.numel(), nth.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         cum = torch.empty_like(nth)
         total = torch.empty((1,), dtype=torch.int32, device=dev)
         nbytes = lib().gi2d_scan_workspace_bytes(N)
@@ -197,7 +218,7 @@ def rasterize_sum_forward(tile_bounds, block, img_size, gaussian_ids_sorted: Ten
         raise RuntimeError(f"tile_bins has {bins.shape[0]} rows but the image has {TX * TY} tiles "
                            "(the reference reads out of bounds here, quirk Q4)")
     dev = xys.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         out = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
         Ts = torch.empty((H, W), dtype=torch.float32, device=dev)
         fidx = torch.empty((H, W), dtype=torch.int32, device=dev)
@@ -223,7 +244,7 @@ def rasterize_sum_backward(img_height: int, img_width: int, BLOCK_H: int, BLOCK_
     H, W = int(img_height), int(img_width)
     TX, TY = (W + 15) // 16, (H + 15) // 16
     N, dev = xys.size(0), xys.device
-    with torch.cuda.device(dev):
+    with _guard(dev):
         v_xy = torch.empty((N, 2), dtype=torch.float32, device=dev)
         v_conic = torch.empty((N, 3), dtype=torch.float32, device=dev)
         v_colors = torch.empty((N, 3), dtype=torch.float32, device=dev)
@@ -258,7 +279,7 @@ def project_backward_autograd(mode: str, num_points: int, params, img_height: in
                                                  want_cov2d=False)[1:]
         return project_gaussians_2d_scale_rot_backward(N, None, params[0], params[1], img_height, img_width, radii, conics,
                                                        v_xy, None, v_conic, want_cov2d=False)[1:]
-    with torch.cuda.device(dev):
+    with _guard(dev):
         v_mean2d = torch.empty((N, 2), dtype=torch.float32, device=dev)
         if mode == "cholesky":
             v_L = torch.empty((N, 3), dtype=torch.float32, device=dev)

@@ -77,7 +77,7 @@ def rasterize_gaussians_sum(
             f"incorrect shape of background color tensor, expected shape {colors.shape[-1]}"
         )
     else:
-        background = torch.ones(colors.shape[-1], dtype=torch.float32, device=colors.device)
+        background = _default_background(colors)
     if xys.ndimension() != 2 or xys.size(1) != 2:
         raise ValueError("xys must have dimensions (N, 2)")
     if colors.ndimension() != 2:
@@ -87,6 +87,21 @@ def rasterize_gaussians_sum(
         colors.contiguous(), opacity.contiguous(), img_height, img_width, BLOCK_H, BLOCK_W, background.contiguous(),
         return_alpha,
     )
+
+
+_ones_cache: dict = {}
+
+
+def _default_background(colors: Tensor) -> Tensor:
+    """The reference allocates torch.ones(C) on every call (rasterize_sum.py:61-63); the value is a constant nobody
+    writes to, so one tensor per (device, C) is kept (saves an allocation and a fill kernel per call)."""
+    key = (colors.device, colors.shape[-1])
+    bg = _ones_cache.get(key)
+    if bg is None:
+        bg = torch.ones(colors.shape[-1], dtype=torch.float32, device=colors.device)
+        if not (colors.is_cuda and torch.cuda.is_current_stream_capturing()):     # a graph-pool tensor must not outlive its graph
+            _ones_cache[key] = bg
+    return bg
 
 
 def _align(v: int, a: int = 256) -> int:
@@ -130,7 +145,7 @@ class _RasterizeGaussiansSum(Function):
             tile_bins, packed = ctx.saved_tensors
             dev = packed.device
             v_out = _C._f32(v_out_img.contiguous(), "v_out_img")
-            with torch.cuda.device(dev):
+            with _C._guard(dev):
                 grads = torch.empty((N, 12), dtype=torch.float32, device=dev)     # 48-byte rows: vector reductions
                 check(lib().gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(),
                                                        v_out.data_ptr(), grads.data_ptr(), _C._stream(dev)),
@@ -191,7 +206,7 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
     ctx.opacity_shape = opacity.shape
     key = (dev.index, N, TX, TY)
     strict = not (_sync_free or torch.cuda.is_current_stream_capturing())
-    with torch.cuda.device(dev):
+    with _C._guard(dev):
         while True:
             cap = _capacity.get(key)
             if cap is None:

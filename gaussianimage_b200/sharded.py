@@ -64,7 +64,7 @@ class RowShardedRenderer:
         N = xys.size(0)
         if self._cap is None:
             self._cap = max(int(4 * N * (r1 - r0) / max(self.TY, 1)) + (1 << 14), 1 << 14)
-        with torch.cuda.device(dev):
+        with _C._guard(dev):
             stream = _C._stream(dev)
             while True:
                 cap = self._cap

@@ -1,0 +1,59 @@
+"""Host-side cost of the eager operator path: cProfile over fit steps in sync-free mode (the GPU never makes the host
+wait, so wall time per step = host time per step).  python tools/host_prof.py [C2] [steps]"""
+import cProfile
+import pstats
+import sys
+import time
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import torch
+
+import gaussianimage_b200 as G
+from gaussianimage_b200.synth import make_config
+
+cfg = sys.argv[1] if len(sys.argv) > 1 else "C2"
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 300
+s = make_config(cfg)
+d = s.to("cuda:0")
+means = d.means2d.clone().requires_grad_(True)
+L = d.cholesky.clone().requires_grad_(True)
+colors = d.colors.clone().requires_grad_(True)
+
+
+def step():
+    xys, depths, radii, conics, nth = G.project_gaussians_2d(means, L, s.H, s.W, s.tile_bounds)
+    out = G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, colors, d.opacity, s.H, s.W)
+    loss = torch.nn.functional.mse_loss(out, d.gt)
+    return torch.autograd.grad(loss, [means, L, colors])
+
+
+def render():
+    with torch.no_grad():
+        xys, depths, radii, conics, nth = G.project_gaussians_2d(means, L, s.H, s.W, s.tile_bounds)
+        return G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, colors, d.opacity, s.H, s.W)
+
+
+for mode in (False, True):
+    G.set_sync_free(mode)
+    for name, fn in (("fit", step), ("render", render)):
+        for _ in range(20):
+            fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            fn()
+        t_host = time.perf_counter() - t0
+        torch.cuda.synchronize()
+        t_all = time.perf_counter() - t0
+        print(f"{name:6s} sync_free={mode}: host {1e6 * t_host / steps:7.1f} us/step, with drain {1e6 * t_all / steps:7.1f} us/step")
+
+G.set_sync_free(True)
+pr = cProfile.Profile()
+pr.enable()
+for _ in range(steps):
+    step()
+pr.disable()
+torch.cuda.synchronize()
+st = pstats.Stats(pr)
+st.sort_stats("tottime").print_stats(28)
