@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
                                                       uint32_t *ctl, uint32_t *scan_state, const float *__restrict__ xys,
                                                       const int *__restrict__ radii, int TX, int TY, int capacity,
                                                       uint32_t *keys_out, int *vals_out, PassPlan plan,
-                                                      int2 *tile_bins_init, int n_bins, int *status_out, int use_ticket, int dbg, int wy0, int wy1) {
+                                                      int2 *tile_bins_init, int n_bins, int *status_out, volatile int *status_host, int use_ticket, int dbg, int wy0, int wy1) {
     __shared__ int s_warp[SCAN_T / 32];
     __shared__ int s_bcast[2];
     __shared__ uint32_t s_hist[FUSED ? MAX_PASSES * RADIX : 1];
@@ -211,6 +211,11 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
             const int over = total > capacity ? 1 : 0;
             ctl[CTL_OVERFLOW] = (uint32_t)over;
             if (status_out) { status_out[0] = total; status_out[1] = over; }
+            if (status_host) {          // mapped pinned host memory: the host polls [0] (preset to -1) instead of synchronising
+                status_host[1] = over;
+                __threadfence_system();
+                status_host[0] = total;
+            }
         }
     }
     if (FUSED && !(dbg & 1)) {
@@ -552,7 +557,7 @@ int gi2d_scan_tiles(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *to
     const int grid = (N + 1023) / 1024;
     const int ticket = all_resident(scan_kernel<false, 1024>, 1024, grid) ? 0 : 1;
     scan_kernel<false, 1024><<<grid, 1024, 0, stream>>>(N, num_tiles_hit, cum_tiles_hit, ctl, state, nullptr, nullptr, 0, 0, 0, nullptr,
-                                                   nullptr, none, nullptr, 0, nullptr, ticket, 0, 0, 0x7fffffff);
+                                                   nullptr, none, nullptr, 0, nullptr, nullptr, ticket, 0, 0, 0x7fffffff);
     if (total_out) cudaMemcpyAsync(total_out, ctl + CTL_N, sizeof(int), cudaMemcpyDefault, stream);
     return cuda_status();
 }
@@ -641,10 +646,10 @@ size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity) {
 //   tile_bins (TX*TY,2) int32: [lo,hi) per tile; EMPTY tiles hold (INT_MAX, 0) until gi2d_raster_sum_fwd_packed
 //   rewrites them to the reference's (0, 0).
 // Precondition (2D path): depths are all zero, so the key is the tile id alone.
-int gi2d_bin_fused_rows(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
-                        const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
-                        int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
-                        int *status_out, cudaStream_t stream) {
+int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
+                               const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
+                               int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
+                               int *status_out, int *status_host, cudaStream_t stream) {
     if (N <= 0 || TX <= 0 || TY <= 0 || capacity <= 0 || ty_begin < 0 || ty_end > TY || ty_begin >= ty_end) return GI2D_ERR_INVALID;
     const int T = TX * TY;
     const FusedLayout L = fused_layout(N, T, capacity);
@@ -663,18 +668,19 @@ int gi2d_bin_fused_rows(int N, int TX, int TY, int ty_begin, int ty_end, const f
     int *v0 = (plan.npass % 2 == 0) ? gids_sorted : vals_b;
     uint32_t *k0 = keys_a;
     const Tuning &tn = tuning();
+    static const int dbg = env_int("GI2D_DBG", 0);
     int2 *bins2 = reinterpret_cast<int2 *>(tile_bins);
 #define GI2D_SCAN(NT)                                                                                                      \
     {                                                                                                                      \
         const int grid = (N + NT - 1) / NT;                                                                                \
         const int ticket = all_resident(scan_kernel<true, NT>, NT, grid) ? 0 : 1;                                          \
         scan_kernel<true, NT><<<grid, NT, 0, stream>>>(N, num_tiles_hit, nullptr, ctl, scan_state, xys, radii, TX, TY,     \
-                                                       capacity, k0, v0, plan, bins2, T, status_out, ticket, env_int("GI2D_DBG", 0),  \
+                                                       capacity, k0, v0, plan, bins2, T, status_out, status_host, ticket, dbg,        \
                                                        ty_begin, ty_end);                                                 \
     }
     if (tn.scan_t == 256) GI2D_SCAN(256) else if (tn.scan_t == 512) GI2D_SCAN(512) else GI2D_SCAN(1024)
 #undef GI2D_SCAN
-    if (env_int("GI2D_DBG", 0) & 4) return cuda_status();      // experiments: scan kernel only
+    if (dbg & 4) return cuda_status();      // experiments: scan kernel only
     PackSrc none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0};
     PackSrc ps{xys, conics, colors, opacities, reinterpret_cast<float4 *>(packed), tile_bins, T};
     const uint32_t *src_k = k0;
@@ -703,6 +709,14 @@ int gi2d_bin_fused_rows(int N, int TX, int TY, int ty_begin, int ty_end, const f
         src_v = dst_v;
     }
     return cuda_status();
+}
+
+int gi2d_bin_fused_rows(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
+                        const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
+                        int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
+                        int *status_out, cudaStream_t stream) {
+    return gi2d_bin_fused_rows_notify(N, TX, TY, ty_begin, ty_end, xys, radii, num_tiles_hit, conics, colors, opacities, capacity, ws,
+                                      ws_bytes, gids_sorted, tile_bins, packed, status_out, nullptr, stream);
 }
 
 int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, const int *num_tiles_hit,

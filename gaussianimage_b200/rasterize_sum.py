@@ -27,7 +27,7 @@ from .utils import _depths_known_zero, bin_and_sort_gaussians, compute_cumulativ
 
 _sync_free = os.environ.get("GI2D_SYNC_FREE", "0") == "1"
 _capacity: dict = {}        # (device index, N, TX, TY) -> intersection capacity of the fused workspace
-_last_status: dict = {}     # device index -> (status tensor (2,) int32, capacity) of the most recent fused call
+_last_status: dict = {}     # device index -> (scratch, status offset, capacity, key) of the most recent fused call
 
 
 def set_sync_free(flag: bool) -> None:
@@ -43,8 +43,8 @@ def check_overflow(device=None) -> int:
     idx = torch.cuda.current_device() if device is None else torch.device(device).index
     if idx not in _last_status:
         return 0
-    status, cap, key = _last_status[idx]
-    n, over = status.tolist()
+    scratch, o_status, cap, key = _last_status[idx]
+    n, over = scratch[o_status:o_status + 8].view(torch.int32).tolist()
     if over:
         _capacity[key] = max(_capacity.get(key, 0), int(n * 1.25) + 1024)
         raise RuntimeError(f"gi2d: {n} tile intersections exceeded the workspace capacity {cap}; "
@@ -166,10 +166,60 @@ class _RasterizeGaussiansSum(Function):
         return (v_xy, None, None, v_conic, None, v_colors, v_opacity, None, None, None, None, None, None)
 
 
-def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap, want_aux=False):
+class _HostStatus:
+    """Ring of {n_isect, overflow} words in mapped pinned host memory.  The first kernel of the fused chain stores the
+    pair there as soon as it knows it (csrc/binning.cu: gi2d_bin_fused_rows_notify) and the host polls the word
+    instead of synchronising the stream: the reference's `.item()` (gsplat/gsplat/utils.py:117, quirk Q12) without the
+    GPU ever waiting for the host, and without the host waiting for more than the scan kernel."""
+    SLOTS = 64
+
+    def __init__(self):
+        self.t = torch.empty((self.SLOTS, 2), dtype=torch.int32).pin_memory()
+        self.np = self.t.numpy()
+        self.base = self.t.data_ptr()
+        self.i = 0
+
+    def acquire(self) -> int:
+        slot = self.i
+        self.i = (slot + 1) % self.SLOTS
+        self.np[slot, 0] = -1
+        return slot
+
+    def wait(self, slot: int):
+        a, spins = self.np, 0
+        while a[slot, 0] == -1:
+            spins += 1
+            if spins % (1 << 20) == 0:            # seconds without an answer: surface a CUDA fault if there is one
+                torch.cuda.synchronize()
+                if a[slot, 0] == -1:
+                    raise RuntimeError("gi2d: the binning chain never published its intersection count")
+        return int(a[slot, 0]), int(a[slot, 1])
+
+
+_host_status = None
+
+
+class FusedResult:
+    """Device tensors of one pass of the fused chain; gids_sorted / status are views made on demand."""
+    __slots__ = ("out_img", "final_Ts", "final_idx", "tile_bins", "packed", "_scratch", "_o_gids", "_o_status", "_cap")
+
+    @property
+    def gids_sorted(self):
+        return self._scratch[self._o_gids:self._o_gids + 4 * self._cap].view(torch.int32)
+
+    @property
+    def status(self):
+        return self._scratch[self._o_status:self._o_status + 8].view(torch.int32)
+
+    def __getitem__(self, k):           # dict-style access used by bench.py / tests
+        return getattr(self, k)
+
+
+def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap, want_aux=False, host_slot=-1):
     """One asynchronous pass of the fused chain (csrc/binning.cu gi2d_bin_fused + csrc/raster.cu packed forward) on the
-    current stream with an intersection capacity `cap`.  Returns a dict of device tensors:
-    out_img, final_Ts/final_idx (or None), tile_bins (T,2), packed (cap*12), gids_sorted (cap), status (2,) = [n, overflow]."""
+    current stream with an intersection capacity `cap`.  Returns a FusedResult: out_img, final_Ts/final_idx (or None),
+    tile_bins (T,2), packed (cap*12), gids_sorted (cap), status (2,) = [n, overflow].  host_slot >= 0 also publishes the
+    status to that slot of the pinned host ring."""
     dev = xys.device
     L = lib()
     N = xys.size(0)
@@ -179,25 +229,28 @@ def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, 
     # one scratch allocation: [workspace | gids_sorted | status]; tile_bins and packed are kept for backward
     o_gids = _align(ws_bytes)
     o_status = o_gids + _align(4 * cap)
-    scratch = torch.empty((o_status + 256,), dtype=torch.uint8, device=dev)
-    tile_bins = torch.empty((TX * TY, 2), dtype=torch.int32, device=dev)
-    packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
+    r = FusedResult()
+    r._scratch = scratch = torch.empty((o_status + 256,), dtype=torch.uint8, device=dev)
+    r._o_gids, r._o_status, r._cap = o_gids, o_status, cap
+    r.tile_bins = tile_bins = torch.empty((TX * TY, 2), dtype=torch.int32, device=dev)
+    r.packed = packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
     base = scratch.data_ptr()
-    check(L.gi2d_bin_fused(N, TX, TY, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(), conics.data_ptr(),
-                           colors.data_ptr(), opacity.data_ptr(), cap, base, ws_bytes, base + o_gids,
-                           tile_bins.data_ptr(), packed.data_ptr(), base + o_status, stream), "bin_fused")
-    out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
-    final_Ts = torch.empty((H, W), dtype=torch.float32, device=dev) if want_aux else None
-    final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if want_aux else None
+    host_ptr = _host_status.base + 8 * host_slot if host_slot >= 0 else 0
+    check(L.gi2d_bin_fused_rows_notify(N, TX, TY, 0, TY, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(),
+                                       conics.data_ptr(), colors.data_ptr(), opacity.data_ptr(), cap, base, ws_bytes,
+                                       base + o_gids, tile_bins.data_ptr(), packed.data_ptr(), base + o_status, host_ptr,
+                                       stream), "bin_fused")
+    r.out_img = out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+    r.final_Ts = final_Ts = torch.empty((H, W), dtype=torch.float32, device=dev) if want_aux else None
+    r.final_idx = final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if want_aux else None
     check(L.gi2d_raster_sum_fwd_packed(TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(), base + o_status,
                                        background.data_ptr(), out_img.data_ptr(), _C._p(final_Ts),
                                        _C._p(final_idx), stream), "rasterize_sum_forward")
-    return dict(out_img=out_img, final_Ts=final_Ts, final_idx=final_idx, tile_bins=tile_bins, packed=packed,
-                gids_sorted=scratch[o_gids:o_gids + 4 * cap].view(torch.int32),
-                status=scratch[o_status:o_status + 8].view(torch.int32))
+    return r
 
 
 def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background, want_aux):
+    global _host_status
     N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
     dev = xys.device
     xys, conics, colors = _C._f32(xys, "xys"), _C._f32(conics, "conics"), _C._f32(colors, "colors")
@@ -206,22 +259,25 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
     ctx.opacity_shape = opacity.shape
     key = (dev.index, N, TX, TY)
     strict = not (_sync_free or torch.cuda.is_current_stream_capturing())
+    if strict and _host_status is None:
+        _host_status = _HostStatus()
     with _C._guard(dev):
         while True:
             cap = _capacity.get(key)
             if cap is None:
                 cap = _capacity[key] = max(4 * N, 1 << 14)
-            r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux)
-            _last_status[dev.index] = (r["status"], cap, key)
+            slot = _host_status.acquire() if strict else -1
+            r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux, slot)
+            _last_status[dev.index] = (r._scratch, r._o_status, cap, key)
             if not strict:
                 break
-            n, over = r["status"].tolist()         # the single device->host read, after everything is enqueued
+            n, over = _host_status.wait(slot)      # published by the scan kernel; everything is already enqueued
             if not over:
                 ctx.num_intersects = n
                 break
             _capacity[key] = int(n * 1.25) + 1024  # truncated: grow and redo
-    ctx.save_for_backward(r["tile_bins"], r["packed"])
-    return r["out_img"], r["final_Ts"]
+    ctx.save_for_backward(r.tile_bins, r.packed)
+    return r.out_img, r.final_Ts
 
 
 def _forward_staged(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity, background):

@@ -127,6 +127,16 @@ int gi2d_bin_fused_rows(int N, int TX, int TY, int ty_begin, int ty_end, const f
                         int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
                         int *status_out, cudaStream_t stream);
 
+/* Same, and additionally publishes {n_isect, overflow} to `status_host` -- MAPPED PINNED HOST memory (may be NULL) -- as
+ * soon as the first kernel of the chain knows them: [1] = overflow, then (after a system-scope fence) [0] = n_isect.
+ * A caller that presets status_host[0] = -1 can poll it instead of synchronising the stream; this is how
+ * rasterize_gaussians_sum replaces the reference's mid-pipeline `.item()` (gsplat/gsplat/utils.py:117, quirk Q12)
+ * without ever making the GPU wait for the host. */
+int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
+                               const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
+                               int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
+                               int *status_out, int *status_host, cudaStream_t stream);
+
 /* ---- accumulated-sum rasterizer --------------------------------------------------------------------------------- */
 
 /* Replaces rasterize_sum_forward (ext.cpp:22 -> bindings.cu:400-469 -> forward.cu:512-627).
