@@ -58,6 +58,7 @@ def make_scene(H: int, W: int, N: int, seed: int = 1, dense: float = 0.0) -> Sce
     g2 = torch.Generator().manual_seed(seed + 1)
     low = torch.rand(1, 3, (H + 15) // 16 + 1, (W + 15) // 16 + 1, generator=g2)
     gt = torch.nn.functional.interpolate(low, size=(H, W), mode="bilinear", align_corners=True)[0].permute(1, 2, 0)
+    gt = torch.round(gt * 255).clamp(0, 255).to(torch.uint8).float() / 255     # 8-bit levels, like a decoded Kodak/DIV2K image
     return Scene(H, W, means.contiguous(), chol.contiguous(), scales.contiguous(), rotation.contiguous(),
                  colors.contiguous(), opacity, gt.contiguous())
 

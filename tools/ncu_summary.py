@@ -1,0 +1,42 @@
+"""Summarise ncu --set full reports (gpurun_out/*.ncu-rep) into a markdown table + profiles/ncu_traffic.json.
+python tools/ncu_summary.py gpurun_out/r01_full_*.ncu-rep > profiles/r01_ncu_full_C2.md"""
+import csv
+import io
+import json
+import subprocess
+import sys
+from pathlib import Path
+
+KEYS = [("gpu__time_duration.sum", "us"), ("dram__bytes_read.sum", "dram rd"), ("dram__bytes_write.sum", "dram wr"),
+        ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "fma pipe %"),
+        ("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "alu pipe %"),
+        ("sm__inst_issued.avg.pct_of_peak_sustained_active", "issue %"),
+        ("sm__warps_active.avg.pct_of_peak_sustained_active", "occupancy %"),
+        ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram %"),
+        ("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smem wavefronts"),
+        ("launch__registers_per_thread", "regs"), ("smsp__inst_executed.sum", "warp insts")]
+UNIT = {"Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Gbyte": 1e9}
+traffic = {}
+print("| kernel | " + " | ".join(k for _, k in KEYS) + " | top stalls (pc samples) |")
+print("|---|" + "---|" * (len(KEYS) + 1))
+for rep in sys.argv[1:]:
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    if len(rows) < 3:
+        continue
+    hdr, units = rows[0], rows[1]
+    idx = {h: i for i, h in enumerate(hdr)}
+    r = rows[-1]                       # last captured launch (steady state)
+    name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "")
+    cells = []
+    for key, _ in KEYS:
+        cells.append(f"{r[idx[key]]} {units[idx[key]]}".strip() if key in idx else "-")
+    stalls = sorted(((float(r[i]), h.replace("smsp__pcsamp_warps_issue_stalled_", "")) for h, i in idx.items()
+                     if h.startswith("smsp__pcsamp_warps_issue_stalled_") and not h.endswith("_not_issued") and r[i]), reverse=True)[:4]
+    print(f"| `{name}` | " + " | ".join(cells) + " | " + ", ".join(f"{n} {int(v)}" for v, n in stalls) + " |")
+    def b(key):
+        return float(r[idx[key]]) * UNIT.get(units[idx[key]], 1.0)
+    short = next((k for k in ("raster_bwd", "raster_fwd", "scan_kernel", "onesweep", "project_fwd", "project_bwd") if k in name), name)
+    traffic[short] = {"dram_bytes": b("dram__bytes_read.sum") + b("dram__bytes_write.sum"), "us": float(r[idx["gpu__time_duration.sum"]]),
+                      "report": Path(rep).name}
+Path("profiles/ncu_traffic.json").write_text(json.dumps(traffic, indent=1) + "\n")
