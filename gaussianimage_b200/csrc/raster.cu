@@ -77,84 +77,169 @@ __device__ __forceinline__ bool record_rect(const float4 &A, const float4 &B, in
     return true;
 }
 
+// NVLS multicast stores (PTX multimem.st): one store, replicated by the switch to every device of the multicast group.
+__device__ __forceinline__ void multimem_st_v4(float *mc, float4 v) {
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st(float *mc, float v) {
+    asm volatile("multimem.st.weak.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
+
+// Forward.  PERSISTENT kernel: a CTA walks the tiles  blockIdx.x, blockIdx.x + gridDim.x, ...  of its range and keeps
+// TWO record stages in shared memory: while tile k is evaluated out of stage (k & 1), the bulk TMA copy of tile
+// k+1's records is already in flight into the other stage (its tile_bins range was fetched one tile earlier still).
+// At 8K (130k sparse tiles) the per-tile chain  range load -> TMA -> evaluate -> store  is latency-bound; the
+// two-deep prefetch takes the first two links off the critical path.
 template <bool TMA, bool AUX>
-__global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int *tile_bins,
+__global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int n_tiles, int *tile_bins,
                                                         const float4 *__restrict__ packed, GatherSrc src,
                                                         const int *__restrict__ d_status,
                                                         const float *__restrict__ background, float *__restrict__ out_img,
-                                                        float *__restrict__ final_Ts, int *__restrict__ final_idx) {
-    __shared__ __align__(128) float4 s_rec[RB * 3];
-    __shared__ __align__(8) uint64_t s_bar;
+                                                        float *__restrict__ final_Ts, int *__restrict__ final_idx,
+                                                        float *out_mc, int vec_ok) {
+    constexpr int NSTAGE = TMA ? 2 : 1;
+    __shared__ __align__(128) float4 s_rec[NSTAGE][RB * 3];
+    __shared__ __align__(8) uint64_t s_bar[NSTAGE];
+    __shared__ int2 s_range[NSTAGE];
     __shared__ uint8_t s_mask[RB];
     __shared__ uint8_t s_list[RB / 32][RB];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = tile_begin + blockIdx.x;
-    const int ty = tile / TX, tx = tile - ty * TX;
-    const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
+    const int stride = gridDim.x;
+    int k = blockIdx.x;                                   // index of the current tile inside [0, n_tiles)
+    if (k >= n_tiles) return;
+    int2 *bins2 = reinterpret_cast<int2 *>(tile_bins);
     // warp -> 8x4 pixel block (2 across, 4 down); lane -> pixel inside it
     const int bx = warp & 1, by = warp >> 1;
-    const int j = tx0 + bx * 8 + (lane & 7), i = ty0 + by * 4 + (lane >> 3);
-    const bool inside = i < H && j < W;
-    const size_t pix = (size_t)i * W + j;
 
-    const int2 range = reinterpret_cast<const int2 *>(tile_bins)[tile];
-    const int lo = range.x;
-    const int cnt = min(range.y - range.x, GI2D_BATCH);          // Q1: only the first 256 sorted intersections count
-    if (TMA && tid == 0 && range.x == 0x7fffffff)                // empty tile left at (INT_MAX, 0) by gi2d_bin_fused:
-        reinterpret_cast<int2 *>(tile_bins)[tile] = make_int2(0, 0);   // canonical (0, 0) like the reference's zero fill
-
-    float r = 0.f, g = 0.f, b = 0.f, T_final = 1.f;   // T is never updated in the sum rasterizer (Q6)
-    int cur = 0;
-    if (cnt > 0) {
-        stage_records<TMA>(s_rec, &s_bar, packed, src, lo, cnt);
-        if (tid < cnt) {
-            int lx0, lx1, ly0, ly1;
-            uint32_t m = 0;
-            if (record_rect(s_rec[3 * tid], s_rec[3 * tid + 1], tx0, ty0, lx0, lx1, ly0, ly1)) {
-                const uint32_t colm = (lx0 <= 7 ? 1u : 0u) | (lx1 >= 8 ? 2u : 0u);      // which 8-wide halves
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-                    if (ly0 <= 4 * q + 3 && ly1 >= 4 * q) m |= colm << (2 * q);       // bit = by*2 + bx
-            }
-            s_mask[tid] = (uint8_t)m;
+    // thread 0 is the producer: fetches ranges two tiles ahead, issues the TMA copy one tile ahead
+    auto fetch_range = [&](int kk) -> int2 {
+        int2 rg = bins2[tile_begin + kk];
+        if (rg.x == 0x7fffffff) {                         // empty tile left at (INT_MAX, 0) by gi2d_bin_fused:
+            rg = make_int2(0, 0);                         // canonical (0, 0) like the reference's zero fill
+            bins2[tile_begin + kk] = rg;
         }
-        __syncthreads();
-        // per-warp compaction of the record indices whose extent touches this warp's pixel block
-        int nlist = 0;
-        for (int c = 0; c < cnt; c += 32) {
-            const int t = c + lane;
-            const bool hit = t < cnt && ((s_mask[t] >> warp) & 1);
-            const unsigned bal = __ballot_sync(0xffffffffu, hit);
-            if (hit) s_list[warp][nlist + __popc(bal & ((1u << lane) - 1))] = (uint8_t)t;
-            nlist += __popc(bal);
+        return rg;
+    };
+    auto issue = [&](int st, int2 rg) {
+        s_range[st] = rg;
+        const int c = min(rg.y - rg.x, GI2D_BATCH);
+        if (c > 0) {
+            mbar_expect_tx(&s_bar[st], (uint32_t)c * 48u);
+            tma_load_1d(s_rec[st], packed + 3 * (size_t)rg.x, (uint32_t)c * 48u, &s_bar[st]);
         }
-        __syncwarp();
-        const float px = (float)j, py = (float)i;
-        for (int k = 0; k < nlist; ++k) {
-            const int t = s_list[warp][k];
-            const float4 A = s_rec[3 * t], B = s_rec[3 * t + 1];
-            const float dx = fsub(A.x, px), dy = fsub(A.y, py);
-            const float sigma = eval_sigma(dx, dy, A.w, B.x, B.y);
-            const float alpha = fminf(fmul(A.z, exp_neg(sigma)), 1.f);
-            if (sigma < 0.f || alpha < GI2D_ALPHA_MIN) continue;          // forward.cu:602-604
-            const float cb = s_rec[3 * t + 2].x;
-            r = ffma(alpha, B.z, r);                                       // forward.cu:607-609
-            g = ffma(alpha, B.w, g);
-            b = ffma(alpha, cb, b);
-            cur = lo + t;                                                  // forward.cu:611
+    };
+    int2 r_next = make_int2(0, 0);
+    if (TMA) {
+        if (tid == 0) {
+            mbar_init(&s_bar[0], 1);
+            mbar_init(&s_bar[NSTAGE - 1], 1);
+            fence_mbar_init();
+            issue(0, fetch_range(k));
+            if (k + stride < n_tiles) r_next = fetch_range(k + stride);
         }
-    } else if (d_status && background && __ldg(d_status) == 0) {
-        // no intersections at all: rasterize_sum.py:121-129 returns ones * background
-        r = __ldg(background); g = __ldg(background + 1); b = __ldg(background + 2);
-        T_final = 0.f;                  // ... and final_Ts = zeros there (rasterize_sum.py:128)
     }
-    if (inside) {
-        out_img[3 * pix] = r; out_img[3 * pix + 1] = g; out_img[3 * pix + 2] = b;
-        if (AUX) {
+    uint32_t phase_bits = 0;                              // bit st = parity of the next completion of s_bar[st]
+
+    for (int it = 0; k < n_tiles; k += stride, ++it) {
+        const int st = TMA ? (it & 1) : 0;
+        if (TMA) {
+            if (tid == 0 && k + stride < n_tiles) {       // stage st^1 was released by the barrier that ended iteration it-1
+                issue(st ^ 1, r_next);
+                if (k + 2 * stride < n_tiles) r_next = fetch_range(k + 2 * stride);
+            }
+        } else if (tid == 0) {
+            s_range[0] = bins2[tile_begin + k];
+        }
+        __syncthreads();                                  // s_range[st] (and the barrier initialisation) visible
+        const int tile = tile_begin + k;
+        const int ty = tile / TX, tx = tile - ty * TX;
+        const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
+        const int j = tx0 + bx * 8 + (lane & 7), i = ty0 + by * 4 + (lane >> 3);
+        const bool inside = i < H && j < W;
+        const size_t pix = (size_t)i * W + j;
+        const int2 range = s_range[st];
+        const int lo = range.x;
+        const int cnt = min(range.y - range.x, GI2D_BATCH);          // Q1: only the first 256 sorted intersections count
+        const float4 *rec = s_rec[st];
+
+        float r = 0.f, g = 0.f, b = 0.f, T_final = 1.f;   // T is never updated in the sum rasterizer (Q6)
+        int cur = 0;
+        if (cnt > 0) {
+            if (TMA) {
+                mbar_wait(&s_bar[st], (phase_bits >> st) & 1u);
+                phase_bits ^= 1u << st;
+            } else {
+                stage_records<false>(s_rec[0], &s_bar[0], packed, src, lo, cnt);
+            }
+            if (tid < cnt) {
+                int lx0, lx1, ly0, ly1;
+                uint32_t m = 0;
+                if (record_rect(rec[3 * tid], rec[3 * tid + 1], tx0, ty0, lx0, lx1, ly0, ly1)) {
+                    const uint32_t colm = (lx0 <= 7 ? 1u : 0u) | (lx1 >= 8 ? 2u : 0u);      // which 8-wide halves
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (ly0 <= 4 * q + 3 && ly1 >= 4 * q) m |= colm << (2 * q);       // bit = by*2 + bx
+                }
+                s_mask[tid] = (uint8_t)m;
+            }
+            __syncthreads();
+            // per-warp compaction of the record indices whose extent touches this warp's pixel block
+            int nlist = 0;
+            for (int c = 0; c < cnt; c += 32) {
+                const int t = c + lane;
+                const bool hit = t < cnt && ((s_mask[t] >> warp) & 1);
+                const unsigned bal = __ballot_sync(0xffffffffu, hit);
+                if (hit) s_list[warp][nlist + __popc(bal & ((1u << lane) - 1))] = (uint8_t)t;
+                nlist += __popc(bal);
+            }
+            __syncwarp();
+            const float px = (float)j, py = (float)i;
+            for (int q = 0; q < nlist; ++q) {
+                const int t = s_list[warp][q];
+                const float4 A = rec[3 * t], B = rec[3 * t + 1];
+                const float dx = fsub(A.x, px), dy = fsub(A.y, py);
+                const float sigma = eval_sigma(dx, dy, A.w, B.x, B.y);
+                const float alpha = fminf(fmul(A.z, exp_neg(sigma)), 1.f);
+                if (sigma < 0.f || alpha < GI2D_ALPHA_MIN) continue;          // forward.cu:602-604
+                const float cb = rec[3 * t + 2].x;
+                r = ffma(alpha, B.z, r);                                       // forward.cu:607-609
+                g = ffma(alpha, B.w, g);
+                b = ffma(alpha, cb, b);
+                cur = lo + t;                                                  // forward.cu:611
+            }
+        } else if (d_status && background && __ldg(d_status) == 0) {
+            // no intersections at all: rasterize_sum.py:121-129 returns ones * background
+            r = __ldg(background); g = __ldg(background + 1); b = __ldg(background + 2);
+            T_final = 0.f;                  // ... and final_Ts = zeros there (rasterize_sum.py:128)
+        }
+        // Epilogue.  A tile that lies fully inside the image leaves as 16 rows x 12 float4 (one 192-byte run per row)
+        // staged through shared memory; with `out_mc` (the NVLS multicast alias of a symmetric frame buffer) every store
+        // is a `multimem.st`, which the NVSwitch replicates into the frame buffer of EVERY rank -- the all-gather of a
+        // row-sharded render happens inside the rasterizer.
+        if (vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H) {          // uniform over the CTA
+            __syncthreads();                                                    // stage st is free: every warp left its loop
+            float *s_out = reinterpret_cast<float *>(s_rec[st]);
+            const int lp = (by * 4 + (lane >> 3)) * GI2D_TILE + bx * 8 + (lane & 7);
+            s_out[3 * lp] = r; s_out[3 * lp + 1] = g; s_out[3 * lp + 2] = b;
+            __syncthreads();
+            if (tid < 192) {
+                const int row = tid / 12, q = tid - row * 12;
+                const float4 v = reinterpret_cast<const float4 *>(s_out)[tid];
+                const size_t off = ((size_t)(ty0 + row) * W + tx0) * 3 + 4 * q;
+                if (out_mc) multimem_st_v4(out_mc + off, v);
+                else *reinterpret_cast<float4 *>(out_img + off) = v;
+            }
+        } else if (inside) {
+            if (out_mc) { multimem_st(out_mc + 3 * pix, r); multimem_st(out_mc + 3 * pix + 1, g); multimem_st(out_mc + 3 * pix + 2, b); }
+            else { out_img[3 * pix] = r; out_img[3 * pix + 1] = g; out_img[3 * pix + 2] = b; }
+        }
+        if (AUX && inside) {
             final_Ts[pix] = T_final;
             final_idx[pix] = cur;
         }
+        if (TMA) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes to the stage (s_out) before the next TMA into it
+        __syncthreads();     // stage st, s_mask and s_list may be overwritten from here on
     }
 }
 
@@ -361,11 +446,39 @@ static inline int cuda_status() {
     return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
 }
 
+// float4 image stores need 16-byte aligned rows: W % 4 == 0 and an aligned base (nullptr counts as aligned).
+static inline int vec_ok(int W, const void *base) { return (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0); }
+
 // The rasterizers are limited to 4 CTAs/SM by registers; ask for the shared-memory carve-out that lets 4 of them fit.
 template <typename K>
 static void prefer_shared(K kernel) {
     cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 }
+// Persistent forward grid: as many CTAs as are co-resident (SMs x occupancy), never more than there are tiles.
+template <typename K>
+static int fwd_grid(K kernel, int n_tiles) {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    static const void *keys[8];
+    static int vals[8], used = 0;
+    const void *key = reinterpret_cast<const void *>(kernel);
+    int per_sm = 0;
+    for (int i = 0; i < used; ++i)
+        if (keys[i] == key) per_sm = vals[i];
+    if (!per_sm) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RB, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        if (used < 8) { keys[used] = key; vals[used] = per_sm; ++used; }
+        cudaGetLastError();
+    }
+    const int g = sms * per_sm;
+    return n_tiles < g ? n_tiles : g;
+}
+
 static void init_once() {
     static bool done = false;
     if (done) return;
@@ -389,26 +502,34 @@ int gi2d_raster_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, co
     if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0) return GI2D_ERR_INVALID;
     GatherSrc src{gids_sorted, xys, conics, colors, opacities};
     if (final_Ts && final_idx)
-        raster_fwd_kernel<false, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, 0, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx);
+        raster_fwd_kernel<false, true><<<fwd_grid(raster_fwd_kernel<false, true>, TX * TY), RB, 0, stream>>>(TX, W, H, 0, TX * TY, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx, nullptr, vec_ok(W, out_img));
     else
-        raster_fwd_kernel<false, false><<<TX * TY, RB, 0, stream>>>(TX, W, H, 0, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, nullptr, nullptr);
+        raster_fwd_kernel<false, false><<<fwd_grid(raster_fwd_kernel<false, false>, TX * TY), RB, 0, stream>>>(TX, W, H, 0, TX * TY, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, nullptr, nullptr, nullptr, vec_ok(W, out_img));
     return cuda_status();
 }
 
 // Forward over the packed records of gi2d_bin_fused (bulk-TMA staging).  d_status[0] == 0 (no intersections
 // anywhere) makes the kernel write `background` instead, as rasterize_sum.py:121-129 does.
+int gi2d_raster_sum_fwd_packed_rows_mc(int TX, int TY, int W, int H, int ty_begin, int ty_end, int *tile_bins,
+                                       const float *packed, const int *d_status, const float *background, float *out_img,
+                                       float *out_img_mc, float *final_Ts, int *final_idx, cudaStream_t stream) {
+    if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0 || ty_begin < 0 || ty_end > TY || ty_begin >= ty_end) return GI2D_ERR_INVALID;
+    const int vok = vec_ok(W, out_img) && vec_ok(W, out_img_mc);
+    GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
+    const float4 *p = reinterpret_cast<const float4 *>(packed);
+    const int nt = (ty_end - ty_begin) * TX, first = ty_begin * TX;
+    if (final_Ts && final_idx)
+        raster_fwd_kernel<true, true><<<fwd_grid(raster_fwd_kernel<true, true>, nt), RB, 0, stream>>>(TX, W, H, first, nt, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx, out_img_mc, vok);
+    else
+        raster_fwd_kernel<true, false><<<fwd_grid(raster_fwd_kernel<true, false>, nt), RB, 0, stream>>>(TX, W, H, first, nt, tile_bins, p, src, d_status, background, out_img, nullptr, nullptr, out_img_mc, vok);
+    return cuda_status();
+}
+
 int gi2d_raster_sum_fwd_packed_rows(int TX, int TY, int W, int H, int ty_begin, int ty_end, int *tile_bins,
                                     const float *packed, const int *d_status, const float *background, float *out_img,
                                     float *final_Ts, int *final_idx, cudaStream_t stream) {
-    if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0 || ty_begin < 0 || ty_end > TY || ty_begin >= ty_end) return GI2D_ERR_INVALID;
-    GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
-    const float4 *p = reinterpret_cast<const float4 *>(packed);
-    const int grid = (ty_end - ty_begin) * TX, first = ty_begin * TX;
-    if (final_Ts && final_idx)
-        raster_fwd_kernel<true, true><<<grid, RB, 0, stream>>>(TX, W, H, first, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx);
-    else
-        raster_fwd_kernel<true, false><<<grid, RB, 0, stream>>>(TX, W, H, first, tile_bins, p, src, d_status, background, out_img, nullptr, nullptr);
-    return cuda_status();
+    return gi2d_raster_sum_fwd_packed_rows_mc(TX, TY, W, H, ty_begin, ty_end, tile_bins, packed, d_status, background, out_img,
+                                              nullptr, final_Ts, final_idx, stream);
 }
 
 int gi2d_raster_sum_fwd_packed(int TX, int TY, int W, int H, int *tile_bins, const float *packed,

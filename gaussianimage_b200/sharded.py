@@ -4,8 +4,12 @@
   `rank, rank + world, ...` -- `image_shard()`.  No collective touches the hot path.
 * Tile-row-sharded render-only decode of very large frames (BASELINE config 5): every rank holds all Gaussians,
   projects them, bins and rasterizes ONLY the tile rows it owns (csrc: gi2d_bin_fused_rows /
-  gi2d_raster_sum_fwd_packed_rows) straight into its band of a full-size image buffer, and ONE in-place NCCL
-  all-gather over NVLink completes the frame on every rank -- `RowShardedRenderer`.  Bands are equal
+  gi2d_raster_sum_fwd_packed_rows) straight into its band of a full-size image buffer, and the frame is completed on
+  every rank either by ONE in-place NCCL all-gather over NVLink (`fused=False`) or -- the B200/NVSwitch-native form,
+  `fused=True` -- INSIDE the rasterizer: the frame buffer lives in torch symmetric memory and every pixel store is an
+  NVLS multicast store (`multimem.st`, csrc/raster.cu) that the switch replicates into every rank's buffer while the
+  remaining tiles are still being computed; two symmetric-memory barriers per frame replace the collective
+  -- `RowShardedRenderer`.  Bands are equal
   (ceil(TY / world) tile rows, the buffer is padded to world * band rows) so that the all-gather needs no staging
   and no reassembly.  Per-tile order and per-pixel arithmetic do not depend on which rank owns a tile, so the
   gathered frame is bit-identical to the single-GPU one.
@@ -35,7 +39,8 @@ def row_partition(tile_rows: int, world: int) -> List[Tuple[int, int]]:
 class RowShardedRenderer:
     """Render-only (decode) path sharded by tile rows over the ranks of `group` (None = single process)."""
 
-    def __init__(self, H: int, W: int, device, group: Optional[dist.ProcessGroup] = None, emulate_world: int = 0):
+    def __init__(self, H: int, W: int, device, group: Optional[dist.ProcessGroup] = None, emulate_world: int = 0,
+                 fused: bool = False):
         self.H, self.W = int(H), int(W)
         self.TX, self.TY = (self.W + 15) // 16, (self.H + 15) // 16
         self.group = group
@@ -47,7 +52,19 @@ class RowShardedRenderer:
         self.band_rows = (self.TY + self.world - 1) // self.world * 16          # pixel rows per (padded) band
         self.device = torch.device(device)
         # full frame padded to world equal bands; frame() is the (H,W,3) view the caller sees
-        self.buffer = torch.zeros((self.world * self.band_rows, self.W, 3), dtype=torch.float32, device=self.device)
+        shape = (self.world * self.band_rows, self.W, 3)
+        self.fused, self._mc, self._hdl = False, 0, None
+        if fused and self.world > 1 and not emulate_world:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.buffer = symm_mem.empty(shape, dtype=torch.float32, device=self.device)
+            self._hdl = symm_mem.rendezvous(self.buffer, group if group is not None else dist.group.WORLD)
+            self._mc = int(self._hdl.multicast_ptr or 0)
+            if not self._mc:
+                raise RuntimeError("gi2d: fused row-sharded rendering needs NVLS multicast (symmetric memory multicast_ptr is null)")
+            self.buffer.zero_()
+            self.fused = True
+        else:
+            self.buffer = torch.zeros(shape, dtype=torch.float32, device=self.device)
         self.background = torch.ones(3, dtype=torch.float32, device=self.device)
         self._cap = None
         self.status = None
@@ -58,6 +75,8 @@ class RowShardedRenderer:
     def render_band(self, xys, radii, conics, num_tiles_hit, colors, opacity) -> None:
         """Bin + rasterize this rank's tile rows into its band of the frame buffer (asynchronous, current stream)."""
         r0, r1 = self.bands[self.rank]
+        if self.fused:
+            self._hdl.barrier(channel=0)        # every rank is done reading the previous frame before anyone overwrites it
         if r0 >= r1:
             return
         L, dev = lib(), self.device
@@ -81,9 +100,9 @@ class RowShardedRenderer:
                                             ws_bytes, self._gids.data_ptr(), self._bins.data_ptr(), self._packed.data_ptr(),
                                             self.status.data_ptr(), stream), "bin_fused_rows")
                 # H here is the padded buffer height so that every pixel row of the band exists
-                check(L.gi2d_raster_sum_fwd_packed_rows(self.TX, self.TY, self.W, self.buffer.shape[0], r0, r1, self._bins.data_ptr(),
-                                                        self._packed.data_ptr(), 0, 0, self.buffer.data_ptr(), 0, 0, stream),
-                      "rasterize_sum_forward (rows)")
+                check(L.gi2d_raster_sum_fwd_packed_rows_mc(self.TX, self.TY, self.W, self.buffer.shape[0], r0, r1, self._bins.data_ptr(),
+                                                           self._packed.data_ptr(), 0, 0, self.buffer.data_ptr(), self._mc, 0, 0,
+                                                           stream), "rasterize_sum_forward (rows)")
                 if torch.cuda.is_current_stream_capturing() or getattr(self, "_cap_checked", False):
                     break
                 n, over = self.status.tolist()
@@ -93,8 +112,11 @@ class RowShardedRenderer:
                 self._cap = int(n * 1.25) + 1024
 
     def gather(self) -> torch.Tensor:
-        """In-place all-gather of the bands (every rank contributes buffer[rank*band : (rank+1)*band])."""
-        if self.world > 1 and dist.is_initialized():
+        """Completes the frame on every rank: fused mode = a barrier (the multicast stores already delivered every band
+        everywhere); otherwise an in-place all-gather (every rank contributes buffer[rank*band : (rank+1)*band])."""
+        if self.fused:
+            self._hdl.barrier(channel=1)
+        elif self.world > 1 and dist.is_initialized():
             mine = self.buffer[self.rank * self.band_rows: (self.rank + 1) * self.band_rows]
             dist.all_gather_into_tensor(self.buffer, mine, group=self.group)
         return self.frame()

@@ -158,6 +158,15 @@ int gi2d_raster_sum_fwd_packed_rows(int TX, int TY, int W, int H, int ty_begin, 
                                     const float *packed, const int *d_status, const float *background, float *out_img,
                                     float *final_Ts, int *final_idx, cudaStream_t stream);
 
+/* Row-sharded variant with the all-gather FUSED into the rasterizer: `out_img_mc` is the NVLS multicast address of a
+ * symmetric frame buffer (same layout as out_img on every rank; e.g. torch symmetric memory's `multicast_ptr`); every
+ * pixel store is a `multimem.st`, which the NVSwitch replicates into the buffer of every rank of the multicast group
+ * (including this one).  out_img (this rank's own replica) is then only used for alignment checks.  The caller
+ * synchronises the ranks (a barrier after the kernel) before anybody reads the frame.  NULL = plain local stores. */
+int gi2d_raster_sum_fwd_packed_rows_mc(int TX, int TY, int W, int H, int ty_begin, int ty_end, int *tile_bins,
+                                       const float *packed, const int *d_status, const float *background, float *out_img,
+                                       float *out_img_mc, float *final_Ts, int *final_idx, cudaStream_t stream);
+
 /* Replaces rasterize_sum_backward (ext.cpp:23 -> bindings.cu:706-779 -> backward.cu:696-862).
  * v_out (H,W,3).  Outputs v_xy (N,2), v_conic (N,3), v_colors (N,3), v_opacity (N,1) are zeroed by the call.
  * final_idx is accepted for parity and may be NULL.  fp32 atomic accumulation (order-nondeterministic, as in the
