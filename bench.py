@@ -510,10 +510,9 @@ def run_b200(args):
         cpu = {"value": rate, "unit": "frames/s" if render_only else UNIT, "cores": os.cpu_count(), "kind": "port",
                "sample": f"{k} full steps of the same workload in {dt:.1f} s (oracle/gi2d_oracle.c, OpenMP, all host threads)"}
 
-    # our kernels per step: project_fwd, scan+emit, onesweep pass(es), raster_fwd [, raster_bwd, project_bwd]
-    T_ = ((W + 15) // 16) * ((H + 15) // 16)
-    n_pass = max(1, ((max(T_, 2) - 1).bit_length() + 7) // 8)
-    launches_per_step = 3 + n_pass + (0 if render_only else 2)
+    # our kernels per step: project_fwd, binning kernel(s), raster_fwd [, raster_bwd, project_bwd]
+    from gaussianimage_b200._lib import lib as _gi2d_lib
+    launches_per_step = 2 + _gi2d_lib().gi2d_bin_fused_kernel_count(N, (W + 15) // 16, (H + 15) // 16) + (0 if render_only else 2)
     line = {
         "metric": "render FPS @768x512, 70k Gaussians" if render_only else METRIC,
         "value": world * K / (total_ms / 1e3), "unit": "frames/s" if render_only else UNIT, "n_gpus": world, "steps": K, "warmup": Wm,

@@ -19,6 +19,7 @@
 // preceding blocks' digit counts, and scatters.  Stability + ascending-gid emission order gives the per-tile
 // ascending-gid order the reference gets from cub (quirk Q2).  All of this is HBM/L2-bound integer work.
 #include "gi2d_common.cuh"
+#include <cooperative_groups.h>
 #include <stdlib.h>
 
 namespace gi2d {
@@ -453,6 +454,235 @@ __global__ void __launch_bounds__(SB) tile_bins_kernel(int n, const KeyT *__rest
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// One-kernel binning for images of at most 4096 tiles (every GaussianImage fitting configuration: 768x512 has 1536
+// tiles, 1020x678 has 2752): counting sort by tile, stable in Gaussian id, in ONE cooperative launch whose blocks meet
+// at two grid-wide barriers.  Replaces memset + scan + two onesweep passes; needs no zero-initialised memory.
+//   phase 1  a block owns NT consecutive Gaussians, a warp 32 of them; the warp walks its (Gaussian, tile) pairs in
+//            emission order (forward.cu:115-134: Gaussian-major, tile-row-major) and counts them per tile in its own
+//            row of byte counters (a Gaussian hits a tile at most once, so a count is <= 32);
+//   phase 2  per tile: the counts of the warps become exclusive prefixes (bytes inside a group of 8 warps, 16-bit
+//            across the groups), the block total goes to row `block` of a global (blocks x T) matrix;  grid barrier;
+//   phase 3a every warp of the grid takes 4 tile columns of that matrix and scans them over the blocks, in place
+//            (O(blocks x T) traffic in total);  grid barrier;
+//   phase 3b per block: exclusive scan of the tile totals in tile order = first slot of every tile; plus the block's
+//            row of the matrix = first slot of this block inside every tile; block 0 writes tile_bins and status;
+//   phase 4  the warp walks its pairs again in the same order and writes gid and the 48-byte packed record at
+//            slot = tile base + preceding blocks + preceding warps + rank inside the warp (match_any).
+// Stability in (block, warp, emission order) = ascending Gaussian id per tile, the order the reference gets (Q2).
+// Grid barriers cost microseconds only while there is at most one block per SM, so the block shape NT (256/512/1024)
+// is picked as the smallest that keeps the grid within the SM count.
+constexpr int SMALL_T = 1024;                 // largest block shape: threads per block = Gaussians per block
+
+struct SmallArgs {
+    int N, TX, TY, T, capacity;
+    const float *xys;
+    const int *radii, *nth;
+    const float *conics, *colors, *opac;
+    uint32_t *mat;            // (gridDim.x, Tpad): block totals per tile, then (in place) the totals of the preceding blocks
+    uint32_t *tot;            // (Tpad): totals over all blocks
+    uint32_t *ctl;            // zeroed control block: [CTL_SCAN_TICKET] is the grid-barrier counter
+    int *gids_sorted, *tile_bins;
+    float4 *packed;
+    int *status_out;
+    volatile int *status_host;
+    int dbg;                  // experiments: stop after phase 1 / 2 / 3 (bits 8 / 16 / 32)
+};
+
+// Calls f(tile, gid_or_0, owner_lane, active) for every (Gaussian, tile) pair of the warp, 32 pairs per round, in
+// emission order.  All 32 lanes call f in every round (f may use warp-wide primitives).
+template <typename F>
+__device__ __forceinline__ void warp_pairs(int cnt, int x0, int w, int y0, int TX, int gid, F f) {
+    const int lane = threadIdx.x & 31;
+    const int incl = warp_incl_scan(cnt, lane);
+    const int excl = incl - cnt;
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    for (int k0 = 0; k0 < total; k0 += 32) {
+        const int k = k0 + lane;
+        int lo = 0, hi = 31;
+#pragma unroll
+        for (int it = 0; it < 5; ++it) {      // smallest lane whose inclusive count exceeds k
+            const int mid = (lo + hi) >> 1;
+            const int v = __shfl_sync(0xffffffffu, incl, mid);
+            if (v > k) hi = mid; else lo = mid + 1;
+        }
+        const int g = min(lo, 31);
+        const int m = k - __shfl_sync(0xffffffffu, excl, g);
+        const int gw = __shfl_sync(0xffffffffu, w, g);
+        const int gx0 = __shfl_sync(0xffffffffu, x0, g), gy0 = __shfl_sync(0xffffffffu, y0, g);
+        const int ggid = __shfl_sync(0xffffffffu, gid, g);
+        const int row = m / gw;
+        const int tile = (gy0 + row) * TX + gx0 + (m - row * gw);
+        f(tile, ggid, g, k < total);
+    }
+}
+
+template <int TBITS, int NT>
+__global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
+    constexpr int TP = 1 << TBITS;                         // padded tile count
+    constexpr int SMALL_WARPS = NT / 32, NGRP = SMALL_WARPS / 8;
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    unsigned char (*s_cnt)[TP] = reinterpret_cast<unsigned char (*)[TP]>(s_raw);                       // [32][TP]
+    unsigned short (*s_grp)[TP] = reinterpret_cast<unsigned short (*)[TP]>(s_raw + SMALL_WARPS * TP);  // [NGRP][TP]
+    int *s_base = reinterpret_cast<int *>(s_raw + SMALL_WARPS * TP + NGRP * TP * 2);                      // [TP]
+    __shared__ int s_warp[NT / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nb = gridDim.x, b = blockIdx.x;
+
+    {   // zero the byte counters (16 bytes per store)
+        uint4 *z = reinterpret_cast<uint4 *>(s_raw);
+        for (int k = tid; k < SMALL_WARPS * TP / 16; k += NT) z[k] = make_uint4(0, 0, 0, 0);
+    }
+    const int i = b * NT + tid;
+    int cnt = 0, x0 = 0, w = 1, y0 = 0, area = 0;
+    // every load of the kernel's input is issued here, independent of the others; the record fields are only consumed
+    // in phase 4, their latency hides behind phases 1-3
+    float rx = 0.f, ry = 0.f, ro = 0.f, rcx = 0.f, rcy = 0.f, rcz = 0.f, rr = 0.f, rg = 0.f, rb = 0.f;
+    if (i < a.N) {
+        const size_t g = (size_t)i;
+        const int nth = __ldg(a.nth + i), rad = __ldg(a.radii + i);
+        rx = __ldg(a.xys + 2 * g); ry = __ldg(a.xys + 2 * g + 1);
+        rcx = __ldg(a.conics + 3 * g); rcy = __ldg(a.conics + 3 * g + 1); rcz = __ldg(a.conics + 3 * g + 2);
+        rr = __ldg(a.colors + 3 * g); rg = __ldg(a.colors + 3 * g + 1); rb = __ldg(a.colors + 3 * g + 2);
+        ro = __ldg(a.opac + g);
+        if (nth > 0 && rad > 0) {                          // forward.cu:113-114
+            int x1, y1;
+            tile_bbox(rx, ry, (float)rad, a.TX, a.TY, x0, x1, y0, y1);
+            w = x1 - x0;
+            area = max(0, w) * max(0, y1 - y0);
+            if (w <= 0) { w = 1; area = 0; }
+            cnt = min(nth, area);                          // the projections always give num_tiles_hit == area
+        }
+    }
+    __syncthreads();
+    const unsigned lt = (1u << lane) - 1;
+    // ---- phase 1: per-warp, per-tile counts
+    warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int, int, bool active) {
+        const unsigned peers = __match_any_sync(0xffffffffu, active ? tile : -1 - lane);
+        if (active && (peers & lt) == 0) s_cnt[warp][tile] += (unsigned char)__popc(peers);
+        __syncwarp();
+    });
+    __syncthreads();
+    if (a.dbg & 8) return;
+    // ---- phase 2: prefixes over the warps of the block, block totals to the global matrix
+    for (int t = tid; t < TP; t += NT) {
+        int tot = 0;
+#pragma unroll
+        for (int g = 0; g < NGRP; ++g) {
+            s_grp[g][t] = (unsigned short)tot;
+            int run = 0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int c = s_cnt[8 * g + q][t];
+                s_cnt[8 * g + q][t] = (unsigned char)run;  // exclusive inside the group: <= 7 * 32
+                run += c;
+            }
+            tot += run;
+        }
+        a.mat[(size_t)b * TP + t] = (uint32_t)tot;
+    }
+    if (a.dbg & 16) return;
+    // grid-wide barrier (cooperative launch: all blocks are co-resident, the barrier state belongs to the driver, so
+    // this path needs no zero-initialised memory at all)
+    __threadfence();
+    cooperative_groups::this_grid().sync();
+    // ---- phase 3a: exclusive scan over the BLOCKS of every tile column, in place, one warp per 4 tile columns (work
+    // shared by all warps of the grid; O(blocks x tiles) traffic in total instead of every block reading the matrix)
+    {
+        const int gwarp = b * SMALL_WARPS + warp, nwarps = nb * SMALL_WARPS;
+        for (int item = gwarp; item < TP / 4; item += nwarps) {
+            uint4 *col = reinterpret_cast<uint4 *>(a.mat) + item;
+            uint4 carry = make_uint4(0, 0, 0, 0);
+            for (int r0 = 0; r0 < nb; r0 += 128) {             // 4 row batches in flight
+                uint4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int r = r0 + 32 * u + lane;
+                    v[u] = r < nb ? __ldcg(col + (size_t)r * (TP / 4)) : make_uint4(0, 0, 0, 0);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (r0 + 32 * u >= nb) break;
+                    const int r = r0 + 32 * u + lane;
+                    uint4 in = v[u];
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const uint32_t tx = __shfl_up_sync(0xffffffffu, in.x, d), ty = __shfl_up_sync(0xffffffffu, in.y, d);
+                        const uint32_t tz = __shfl_up_sync(0xffffffffu, in.z, d), tw = __shfl_up_sync(0xffffffffu, in.w, d);
+                        if (lane >= d) { in.x += tx; in.y += ty; in.z += tz; in.w += tw; }
+                    }
+                    if (r < nb)
+                        col[(size_t)r * (TP / 4)] = make_uint4(carry.x + in.x - v[u].x, carry.y + in.y - v[u].y,
+                                                              carry.z + in.z - v[u].z, carry.w + in.w - v[u].w);
+                    carry.x += __shfl_sync(0xffffffffu, in.x, 31); carry.y += __shfl_sync(0xffffffffu, in.y, 31);
+                    carry.z += __shfl_sync(0xffffffffu, in.z, 31); carry.w += __shfl_sync(0xffffffffu, in.w, 31);
+                }
+            }
+            if (lane == 0) reinterpret_cast<uint4 *>(a.tot)[item] = carry;
+        }
+    }
+    __threadfence();
+    cooperative_groups::this_grid().sync();
+    if (a.dbg & 64) return;
+    // ---- phase 3b: first slot of every tile = exclusive scan of the totals in tile order + the preceding blocks
+    constexpr int PER = TP / NT;                               // consecutive tiles per thread
+    int tot_t[PER], pre_t[PER], mine = 0;
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+        tot_t[q] = (int)__ldcg(a.tot + tid * PER + q);
+        pre_t[q] = (int)__ldcg(a.mat + (size_t)b * TP + tid * PER + q);
+    }
+#pragma unroll
+    for (int q = 0; q < PER; ++q) mine += tot_t[q];
+    int block_total;
+    const int incl = block_incl_scan<NT>(mine, s_warp, &block_total);
+    {
+        int base = incl - mine;
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+            const int t = tid * PER + q;
+            s_base[t] = base + pre_t[q];
+            if (b == 0 && t < a.T) reinterpret_cast<int2 *>(a.tile_bins)[t] = tot_t[q] > 0 ? make_int2(base, base + tot_t[q]) : make_int2(0, 0);
+            base += tot_t[q];
+        }
+    }
+    if (b == 0 && tid == 0) {
+        const int over = block_total > a.capacity ? 1 : 0;
+        a.ctl[CTL_N] = (uint32_t)block_total;
+        a.ctl[CTL_OVERFLOW] = (uint32_t)over;
+        if (a.status_out) { a.status_out[0] = block_total; a.status_out[1] = over; }
+        if (a.status_host) {
+            a.status_host[1] = over;
+            __threadfence_system();
+            a.status_host[0] = block_total;
+        }
+    }
+    __syncthreads();
+    if (a.dbg & 32) return;
+    // ---- phase 4: scatter gid + packed record to the final slot
+    const int grp = warp >> 3;
+    warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int gid, int owner, bool active) {
+        const unsigned peers = __match_any_sync(0xffffffffu, active ? tile : -1 - lane);
+        int pos = 0;
+        if (active) {
+            const int before = s_cnt[warp][tile];
+            pos = s_base[tile] + (int)s_grp[grp][tile] + before + __popc(peers & lt);
+        }
+        __syncwarp();
+        if (active && (peers & lt) == 0) s_cnt[warp][tile] += (unsigned char)__popc(peers);
+        __syncwarp();
+        const float x = __shfl_sync(0xffffffffu, rx, owner), y = __shfl_sync(0xffffffffu, ry, owner), o = __shfl_sync(0xffffffffu, ro, owner);
+        const float cx = __shfl_sync(0xffffffffu, rcx, owner), cy = __shfl_sync(0xffffffffu, rcy, owner), cz = __shfl_sync(0xffffffffu, rcz, owner);
+        const float r = __shfl_sync(0xffffffffu, rr, owner), gg = __shfl_sync(0xffffffffu, rg, owner), bl = __shfl_sync(0xffffffffu, rb, owner);
+        if (active && pos < a.capacity) {
+            a.gids_sorted[pos] = gid;
+            __stcs(a.packed + 3 * (size_t)pos + 0, make_float4(x, y, o, cx));
+            __stcs(a.packed + 3 * (size_t)pos + 1, make_float4(cy, cz, r, gg));
+            __stcs(a.packed + 3 * (size_t)pos + 2, make_float4(bl, __int_as_float(gid), 0.f, 0.f));
+        }
+    });
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 static inline int cuda_status() {
     const cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
@@ -509,8 +739,30 @@ static bool all_resident(K kernel, int threads, int grid) {
     return grid <= per_sm * sms;
 }
 
+template <typename K>
+static bool all_resident_smem(K kernel, int threads, size_t smem, int grid) {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    static const void *keys[4];
+    static int vals[4], used = 0;
+    const void *key = reinterpret_cast<const void *>(kernel);
+    int per_sm = -1;
+    for (int i = 0; i < used; ++i)
+        if (keys[i] == key) per_sm = vals[i];
+    if (per_sm < 0) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess) per_sm = 0;
+        if (used < 4) { keys[used] = key; vals[used] = per_sm; ++used; }
+        cudaGetLastError();
+    }
+    return grid <= per_sm * sms;
+}
+
 struct FusedLayout {          // carve-up of the caller's workspace for gi2d_bin_fused
-    size_t ctl, scan_state, lookback, zero_bytes, keys_a, keys_b, vals_b, total;
+    size_t ctl, scan_state, lookback, zero_bytes, keys_a, keys_b, vals_b, mat, total;
     int scan_blocks, sort_blocks, npass;
 };
 static FusedLayout fused_layout(int N, int T, int capacity) {
@@ -526,8 +778,47 @@ static FusedLayout fused_layout(int N, int T, int capacity) {
     L.keys_a = o; o += align_up(sizeof(uint32_t) * (size_t)capacity, 256);
     L.keys_b = o; o += align_up(sizeof(uint32_t) * (size_t)capacity, 256);
     L.vals_b = o; o += align_up(sizeof(int) * (size_t)capacity, 256);
+    L.mat = o;                                                         // one-kernel path (T <= 4096): (blocks + 1, Tpad) uint32
+    if (T <= 4096) o += align_up(sizeof(uint32_t) * ((size_t)((N + 255) / 256) + 1) * (T <= 2048 ? 2048 : 4096), 256);
     L.total = o;
     return L;
+}
+
+
+// Chooses the one-kernel path's kernel for (N, T) on the current device, or nullptr when the shape must take the
+// scan + onesweep chain (more than 4096 tiles, or a grid that cannot be co-resident).
+struct SmallPlan { const void *fn; int nt, tp; size_t smem; };
+static SmallPlan small_plan(int N, int T) {
+    SmallPlan p{nullptr, 0, 0, 0};
+    static const int small_ok = env_int("GI2D_SMALL_BIN", 1);
+    static const int small_nt_env = env_int("GI2D_SMALL_NT", 0);
+    if (!small_ok || T > 4096) return p;
+    static int n_sms = 0;
+    if (!n_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    // smallest block shape that keeps the grid within one block per SM (grid barriers are cheap only then)
+    const int small_nt = small_nt_env ? small_nt_env : (N <= 256 * n_sms ? 256 : N <= 512 * n_sms ? 512 : 1024);
+    const int tp = T <= 2048 ? 2048 : 4096;
+    // prefer that shape; fall back to 1024 Gaussians per block when the grid would not be co-resident
+    for (int attempt = 0; attempt < 2 && !p.fn; ++attempt) {
+        const int nt = attempt == 0 ? (small_nt == 512 ? 512 : small_nt == 1024 ? 1024 : 256) : 1024;
+        const int grid = (N + nt - 1) / nt;
+        const size_t smem = (size_t)(nt / 32) * tp + (size_t)(nt / 256) * tp * 2 + (size_t)tp * 4;
+#define GI2D_TRY(TB, NTT)                                                                                                  \
+    if (tp == (1 << TB) && nt == NTT) {                                                                                    \
+        static bool attr = (cudaFuncSetAttribute(bin_small_kernel<TB, NTT>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                                 (NTT / 32) * (1 << TB) + (NTT / 256) * (1 << TB) * 2 + (1 << TB) * 4), true); \
+        (void)attr;                                                                                                        \
+        if (all_resident_smem(bin_small_kernel<TB, NTT>, NTT, smem, grid))                                                 \
+            p = SmallPlan{reinterpret_cast<const void *>(bin_small_kernel<TB, NTT>), NTT, tp, smem};                       \
+    }
+        GI2D_TRY(11, 256) GI2D_TRY(11, 512) GI2D_TRY(11, 1024) GI2D_TRY(12, 256) GI2D_TRY(12, 512) GI2D_TRY(12, 1024)
+#undef GI2D_TRY
+    }
+    return p;
 }
 
 }  // namespace gi2d
@@ -634,6 +925,15 @@ int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *ti
 
 // ---- fused, sync-free chain ---------------------------------------------------------------------------------------
 
+// Number of kernels gi2d_bin_fused launches for this shape on the current device (1 = the one-kernel path; otherwise the
+// scan kernel + one onesweep pass per 8 tile-id bits); the zero-fill of the chain's control block is a memset, not a kernel.
+int gi2d_bin_fused_kernel_count(int N, int TX, int TY) {
+    if (N <= 0 || TX <= 0 || TY <= 0) return 0;
+    const int T = TX * TY;
+    if (small_plan(N, T).fn) return 1;
+    return 1 + make_plan(0, ceil_log2(T > 1 ? T : 2)).npass;
+}
+
 size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity) {
     return fused_layout(N, TX * TY, capacity).total;
 }
@@ -663,12 +963,25 @@ int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, 
     int *vals_b = reinterpret_cast<int *>(base + L.vals_b);
     const PassPlan plan = make_plan(0, ceil_log2(T > 1 ? T : 2));
 
+    // images of at most 4096 tiles, all blocks co-resident: ONE cooperative kernel (counting sort by tile)
+    static const int dbg = env_int("GI2D_DBG", 0);
+    if (ty_begin == 0 && ty_end == TY) {
+        const SmallPlan sp = small_plan(N, T);
+        if (sp.fn) {
+            SmallArgs a{N, TX, TY, T, capacity, xys, radii, num_tiles_hit, conics, colors, opacities,
+                        reinterpret_cast<uint32_t *>(base + L.mat), reinterpret_cast<uint32_t *>(base + L.mat) + (size_t)((N + 255) / 256) * sp.tp,
+                        ctl, gids_sorted, tile_bins, reinterpret_cast<float4 *>(packed), status_out, status_host, dbg};
+            void *args[] = {&a};
+            const cudaError_t e = cudaLaunchCooperativeKernel(sp.fn, dim3((N + sp.nt - 1) / sp.nt), dim3(sp.nt), args, sp.smem, stream);
+            return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
+        }
+    }
+
     cudaMemsetAsync(ws, 0, L.zero_bytes, stream);
     // values ping-pong between gids_sorted and vals_b; start so that the last pass lands in gids_sorted
     int *v0 = (plan.npass % 2 == 0) ? gids_sorted : vals_b;
     uint32_t *k0 = keys_a;
     const Tuning &tn = tuning();
-    static const int dbg = env_int("GI2D_DBG", 0);
     int2 *bins2 = reinterpret_cast<int2 *>(tile_bins);
 #define GI2D_SCAN(NT)                                                                                                      \
     {                                                                                                                      \

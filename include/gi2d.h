@@ -115,6 +115,9 @@ int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *ti
  *   status_out (2) int32: [0] = n_isect, [1] = 1 if n_isect > capacity (outputs truncated; retry with more).
  * Requires all depths == 0 (true for both 2D projections). n_isect < 2^30. */
 size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity);
+/* How many kernels gi2d_bin_fused launches for this shape on the current device: 1 for images of at most 4096 tiles
+ * whose grid is co-resident (one cooperative counting-sort kernel), else 1 + one onesweep pass per 8 tile-id bits. */
+int gi2d_bin_fused_kernel_count(int N, int TX, int TY);
 int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, const int *num_tiles_hit,
                    const float *conics, const float *colors, const float *opacities, int capacity, void *ws,
                    size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed, int *status_out,

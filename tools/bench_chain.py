@@ -79,9 +79,11 @@ def time_graph(fn, reps=30):
     return statistics.median(ts), min(ts)
 
 
+import os
 binning(); fwd(); bwd()
 torch.cuda.synchronize()
-assert status.tolist() == [n, 0]
+if not os.environ.get("GI2D_DBG"):
+    assert status.tolist() == [n, 0]
 for name, fn in (("binning_chain", binning), ("raster_fwd", fwd), ("raster_bwd", bwd), ("project_fwd", pfwd)):
     med, mn = time_graph(fn)
     print(f"{name:16s} median {med:7.2f} us   min {mn:7.2f} us")
