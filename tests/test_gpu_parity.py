@@ -475,3 +475,53 @@ def test_row_sharded_bands_reproduce_the_single_gpu_frame_bit_for_bit(world):
         R.render_band(xys, radii, conics, nth, d.colors, d.opacity)
     torch.cuda.synchronize()
     assert torch.equal(R.frame(), f["out"])
+
+
+# ------------------------------------------------------------------------------------------------ binning variants
+@pytest.mark.parametrize("env", [{"GI2D_SMALL_BIN": "0"}, {"GI2D_SMALL_NT": "256"}, {"GI2D_SMALL_NT": "1024"}],
+                         ids=["onesweep_chain", "one_kernel_nt256", "one_kernel_nt1024"])
+def test_every_binning_path_passes_the_list_and_image_checks(env):
+    """The fused chain has two implementations (one cooperative counting-sort kernel for <= 4096 tiles with three block
+    shapes; scan + onesweep passes otherwise), chosen inside the library.  The choice is read from the environment once
+    per process, so each variant re-runs the list / image / fit-step parity tests in a fresh interpreter."""
+    import os
+    import subprocess
+    import sys
+    sel = "fused_chain_lists or forward_bit_exact or operator_fit_step or zero_intersections or backward_vs_oracle"
+    r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_gpu_parity.py", "-q", "-x", "-m", "gpu", "-k", sel,
+                        "-p", "no:cacheprovider"], env={**os.environ, **env}, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_fused_chain_reports_overflow_and_does_not_write_out_of_bounds():
+    """Capacity smaller than the intersection count: status = [n, 1], slots beyond the capacity stay untouched."""
+    from gaussianimage_b200._lib import check, lib
+    L = lib()
+    s = scene("c1_small")
+    d = s.to(DEV)
+    xys, depths, radii, conics, nth = G.project_gaussians_2d(d.means2d, d.cholesky, s.H, s.W, s.tile_bounds)
+    N, (TX, TY, _) = xys.shape[0], s.tile_bounds
+    n_true = int(nth.sum().item())
+    cap = n_true // 3
+    nbytes = L.gi2d_bin_fused_workspace_bytes(N, TX, TY, cap)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+    guard = 4096
+    gids = torch.full((cap + guard,), -7, dtype=torch.int32, device=DEV)
+    packed = torch.full(((cap + guard) * 12,), -7.0, dtype=torch.float32, device=DEV)
+    bins = torch.empty(TX * TY, 2, dtype=torch.int32, device=DEV)
+    status = torch.empty(2, dtype=torch.int32, device=DEV)
+    check(L.gi2d_bin_fused(N, TX, TY, xys.data_ptr(), radii.data_ptr(), nth.data_ptr(), conics.data_ptr(), d.colors.data_ptr(),
+                           d.opacity.data_ptr(), cap, ws.data_ptr(), nbytes, gids.data_ptr(), bins.data_ptr(), packed.data_ptr(),
+                           status.data_ptr(), torch.cuda.current_stream().cuda_stream), "bin_fused")
+    torch.cuda.synchronize()
+    assert status.tolist() == [n_true, 1]
+    assert (gids[cap:] == -7).all() and (packed[cap * 12:] == -7.0).all()
+    # the operator recovers by itself: strict mode grows the capacity and redoes the pass
+    from gaussianimage_b200 import rasterize_sum as RS
+    RS._capacity[(torch.device(DEV).index, N, TX, TY)] = cap
+    out = G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, d.colors, d.opacity, s.H, s.W)
+    want, _ = oracle_chain(s)
+    amb = O.rasterize_sum_forward(s.H, s.W, _["gaussian_ids_sorted"], _["tile_bins"], _["xys"], _["conics"], _np(s.colors),
+                                  _np(s.opacity), want_ambig=True)[3].astype(bool)
+    assert_image_close(_np(out), want, "image after overflow retry", exclude=amb)
+    assert RS._capacity[(torch.device(DEV).index, N, TX, TY)] > n_true
