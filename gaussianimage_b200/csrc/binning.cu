@@ -641,7 +641,9 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
         for (int q = 0; q < PER; ++q) {
             const int t = tid * PER + q;
             s_base[t] = base + pre_t[q];
-            if (b == 0 && t < a.T) reinterpret_cast<int2 *>(a.tile_bins)[t] = tot_t[q] > 0 ? make_int2(base, base + tot_t[q]) : make_int2(0, 0);
+            // on overflow (n_isect > capacity, reported through status) the ranges are clipped to what was written
+            if (b == 0 && t < a.T)
+                reinterpret_cast<int2 *>(a.tile_bins)[t] = tot_t[q] > 0 ? make_int2(min(base, a.capacity), min(base + tot_t[q], a.capacity)) : make_int2(0, 0);
             base += tot_t[q];
         }
     }
