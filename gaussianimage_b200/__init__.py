@@ -8,7 +8,7 @@ test_quantize.py run unchanged.  There is no CPU fallback.
 """
 from .project_gaussians_2d import project_gaussians_2d
 from .project_gaussians_2d_scale_rot import project_gaussians_2d_scale_rot
-from .rasterize_sum import check_overflow, rasterize_gaussians_sum, set_sync_free
+from .rasterize_sum import check_overflow, rasterize_gaussians_sum, set_memoise_binning, set_sync_free
 from .utils import (
     bin_and_sort_gaussians,
     compute_cov2d_bounds,
@@ -31,4 +31,5 @@ __all__ = [
     "map_gaussian_to_intersects",
     "set_sync_free",
     "check_overflow",
+    "set_memoise_binning",
 ]

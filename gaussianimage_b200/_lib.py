@@ -34,6 +34,7 @@ _SIGNATURES = {
     "gi2d_tile_bins": (_i, [_i, _vp, _i, _vp, _vp]),
     "gi2d_bin_fused_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "gi2d_bin_fused_kernel_count": (_i, [_i, _i, _i]),
+    "gi2d_repack_records": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_bin_fused": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_bin_fused_rows": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_bin_fused_rows_notify": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -823,6 +823,27 @@ static SmallPlan small_plan(int N, int T) {
     return p;
 }
 
+// Records of an EXISTING sorted list with other per-Gaussian attributes: a caller that renders the same geometry several
+// times with different colours (gaussianimage_cholesky.py:81,89,95 -- three rasterize_gaussians_sum calls per forward on
+// the same xys / radii / num_tiles_hit, quirk Q13) re-uses gids_sorted and tile_bins and only rebuilds the 48-byte records.
+__global__ void __launch_bounds__(256) repack_kernel(int capacity, const int *__restrict__ gids_sorted, const int *__restrict__ status,
+                                                      const float *__restrict__ xys, const float *__restrict__ conics,
+                                                      const float *__restrict__ colors, const float *__restrict__ opac,
+                                                      float4 *__restrict__ packed) {
+    const int n = min(__ldg(status), capacity);
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+        const int v = __ldg(gids_sorted + i);
+        const size_t g = (size_t)v;
+        const float x = __ldg(xys + 2 * g), y = __ldg(xys + 2 * g + 1);
+        const float cx = __ldg(conics + 3 * g), cy = __ldg(conics + 3 * g + 1), cz = __ldg(conics + 3 * g + 2);
+        const float r = __ldg(colors + 3 * g), gg = __ldg(colors + 3 * g + 1), b = __ldg(colors + 3 * g + 2);
+        const float o = __ldg(opac + g);
+        __stcs(packed + 3 * (size_t)i + 0, make_float4(x, y, o, cx));
+        __stcs(packed + 3 * (size_t)i + 1, make_float4(cy, cz, r, gg));
+        __stcs(packed + 3 * (size_t)i + 2, make_float4(b, __int_as_float(v), 0.f, 0.f));
+    }
+}
+
 }  // namespace gi2d
 
 using namespace gi2d;
@@ -1041,6 +1062,16 @@ int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, co
     if (TY <= 0) return GI2D_ERR_INVALID;
     return gi2d_bin_fused_rows(N, TX, TY, 0, TY, xys, radii, num_tiles_hit, conics, colors, opacities, capacity, ws, ws_bytes,
                                gids_sorted, tile_bins, packed, status_out, stream);
+}
+
+int gi2d_repack_records(int capacity, const int *gids_sorted, const int *status, const float *xys, const float *conics,
+                        const float *colors, const float *opacities, float *packed, cudaStream_t stream) {
+    if (capacity < 0 || !gids_sorted || !status || !xys || !conics || !colors || !opacities || !packed) return GI2D_ERR_INVALID;
+    if (capacity == 0) return GI2D_OK;
+    const int grid = std::min((capacity + 255) / 256, 8 * 148);
+    repack_kernel<<<grid, 256, 0, stream>>>(capacity, gids_sorted, status, xys, conics, colors, opacities,
+                                            reinterpret_cast<float4 *>(packed));
+    return cuda_status();
 }
 
 }  // extern "C"

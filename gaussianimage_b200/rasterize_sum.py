@@ -249,8 +249,55 @@ def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, 
     return r
 
 
+class _Geometry:
+    """The last binning result per (device, stream): sorted ids, tile ranges, status.  rasterize_gaussians_sum called
+    again with the SAME xys / radii / num_tiles_hit tensors (same storage, same version counters -- the reference model
+    does it three times per forward, gaussianimage_cholesky.py:81,89,95, quirk Q13) only rebuilds the packed records from
+    the new conics / colours / opacities (gi2d_repack_records) and rasterizes; the lists are bit-identical by construction."""
+    __slots__ = ("xys", "radii", "nth", "versions", "shape", "result", "cap", "n_isect")
+
+    def matches(self, xys, radii, nth, shape):
+        return (self.shape == shape and self.xys.data_ptr() == xys.data_ptr() and self.radii.data_ptr() == radii.data_ptr()
+                and self.nth.data_ptr() == nth.data_ptr() and self.versions == (xys._version, radii._version, nth._version))
+
+
+_geometry: dict = {}
+_memoise = True
+geometry_hits = 0          # how many calls re-used a binning result (tests / bench read it)
+
+
+def set_memoise_binning(flag: bool):
+    """Turn the re-use of the previous binning result for identical geometry tensors on / off (default on)."""
+    global _memoise
+    _memoise = bool(flag)
+    _geometry.clear()
+
+
+def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=False):
+    """Rasterize the geometry of a previous fused_chain result with other conics / colours / opacities."""
+    dev = xys.device
+    L = lib()
+    TX, TY = (W + 15) // 16, (H + 15) // 16
+    stream = _C._stream(dev)
+    src, cap = g.result, g.cap
+    r = FusedResult()
+    r._scratch, r._o_gids, r._o_status, r._cap = src._scratch, src._o_gids, src._o_status, cap
+    r.tile_bins = src.tile_bins
+    r.packed = packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
+    base = src._scratch.data_ptr()
+    check(L.gi2d_repack_records(cap, base + src._o_gids, base + src._o_status, xys.data_ptr(), conics.data_ptr(),
+                                colors.data_ptr(), opacity.data_ptr(), packed.data_ptr(), stream), "repack_records")
+    r.out_img = out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+    r.final_Ts = final_Ts = torch.empty((H, W), dtype=torch.float32, device=dev) if want_aux else None
+    r.final_idx = final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if want_aux else None
+    check(L.gi2d_raster_sum_fwd_packed(TX, TY, W, H, r.tile_bins.data_ptr(), packed.data_ptr(), base + src._o_status,
+                                       background.data_ptr(), out_img.data_ptr(), _C._p(final_Ts),
+                                       _C._p(final_idx), stream), "rasterize_sum_forward")
+    return r
+
+
 def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background, want_aux):
-    global _host_status
+    global _host_status, geometry_hits
     N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
     dev = xys.device
     xys, conics, colors = _C._f32(xys, "xys"), _C._f32(conics, "conics"), _C._f32(colors, "colors")
@@ -262,6 +309,15 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
     if strict and _host_status is None:
         _host_status = _HostStatus()
     with _C._guard(dev):
+        gkey = (dev.index, _C._stream(dev))
+        g = _geometry.get(gkey) if _memoise else None
+        if g is not None and g.matches(xys, radii, nth, key):
+            geometry_hits += 1
+            r = fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux)
+            if g.n_isect is not None:
+                ctx.num_intersects = g.n_isect
+            ctx.save_for_backward(r.tile_bins, r.packed)
+            return r.out_img, r.final_Ts
         while True:
             cap = _capacity.get(key)
             if cap is None:
@@ -269,6 +325,7 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
             slot = _host_status.acquire() if strict else -1
             r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux, slot)
             _last_status[dev.index] = (r._scratch, r._o_status, cap, key)
+            n = None
             if not strict:
                 break
             n, over = _host_status.wait(slot)      # published by the scan kernel; everything is already enqueued
@@ -276,6 +333,14 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
                 ctx.num_intersects = n
                 break
             _capacity[key] = int(n * 1.25) + 1024  # truncated: grow and redo
+        if _memoise:
+            g = _Geometry()
+            g.xys, g.radii, g.nth, g.shape = xys.detach(), radii.detach(), nth.detach(), key   # no autograd graph kept alive
+            g.versions = (xys._version, radii._version, nth._version)
+            keep = FusedResult()               # lists only: the image is an autograd output and would pin the whole graph
+            keep._scratch, keep._o_gids, keep._o_status, keep._cap, keep.tile_bins = r._scratch, r._o_gids, r._o_status, cap, r.tile_bins
+            g.result, g.cap, g.n_isect = keep, cap, n
+            _geometry[gkey] = g
     ctx.save_for_backward(r.tile_bins, r.packed)
     return r.out_img, r.final_Ts
 

@@ -118,6 +118,12 @@ size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity);
 /* How many kernels gi2d_bin_fused launches for this shape on the current device: 1 for images of at most 4096 tiles
  * whose grid is co-resident (one cooperative counting-sort kernel), else 1 + one onesweep pass per 8 tile-id bits. */
 int gi2d_bin_fused_kernel_count(int N, int TX, int TY);
+/* The records of an existing sorted list rebuilt from other per-Gaussian attributes (conics / colours / opacities): what
+ * a caller that rasterizes the SAME geometry again with other colours needs instead of a second binning pass
+ * (gaussianimage_cholesky.py:81,89,95 calls rasterize_gaussians_sum three times per forward on one projection, Q13).
+ * gids_sorted / status are outputs of gi2d_bin_fused for that geometry; writes min(status[0], capacity) records. */
+int gi2d_repack_records(int capacity, const int *gids_sorted, const int *status, const float *xys, const float *conics,
+                        const float *colors, const float *opacities, float *packed, cudaStream_t stream);
 int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, const int *num_tiles_hit,
                    const float *conics, const float *colors, const float *opacities, int capacity, void *ws,
                    size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed, int *status_out,

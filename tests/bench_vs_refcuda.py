@@ -38,6 +38,8 @@ class RefPipeline:
     def __init__(self, d, s, flavor, param):
         self.d, self.s, self.L, self.param = d, s, refcuda.lib(flavor), param
         self.bg = torch.ones(3)          # host: passed to the kernels by value
+        self.alt_colors = d.colors.flip(0).contiguous() * 0.5
+        self.one_colors = torch.ones_like(d.colors)
 
     def project(self):
         d, s, dev = self.d, self.s, self.d.means2d.device
@@ -54,8 +56,15 @@ class RefPipeline:
                                             _p(radii), _p(conics), _p(nth))
         return xys, depths, radii, conics, nth
 
-    def rasterize(self, xys, depths, radii, conics, nth):
+    def model_forward(self):
+        """gaussianimage_cholesky.py:76-98: one projection, three rasterize_gaussians_sum calls (Q13)."""
+        pr = self.project()
+        c = self.d.colors
+        return [self.rasterize(*pr, colors=k)[0] for k in (c, self.alt_colors, self.one_colors)]
+
+    def rasterize(self, xys, depths, radii, conics, nth, colors=None):
         d, s, dev = self.d, self.s, self.d.means2d.device
+        colors = d.colors if colors is None else colors
         N, H, W = xys.shape[0], s.H, s.W
         TX, TY = s.tile_bounds[:2]
         cum = torch.cumsum(nth, dim=0, dtype=torch.int32)                    # utils.py:116
@@ -69,7 +78,7 @@ class RefPipeline:
         self.L.ref_get_tile_bin_edges(n, _p(ids_s), _p(bins))
         out, Ts = torch.zeros(H, W, 3, device=dev), torch.zeros(H, W, device=dev)   # bindings.cu:443-451
         fidx = torch.zeros(H, W, dtype=torch.int32, device=dev)
-        self.L.ref_rasterize_sum_fwd(TX, TY, W, H, _p(gids_s), _p(bins), _p(xys), _p(conics), _p(d.colors), _p(d.opacity), _p(self.bg),
+        self.L.ref_rasterize_sum_fwd(TX, TY, W, H, _p(gids_s), _p(bins), _p(xys), _p(conics), _p(colors), _p(d.opacity), _p(self.bg),
                                      _p(out), _p(Ts), _p(fidx))
         return out, (gids_s, bins, Ts, fidx)
 
@@ -107,6 +116,8 @@ class OurPipeline:
         self.d, self.s, self.param = d, s, param
         self.means = d.means2d.clone().requires_grad_(True)
         self.colors = d.colors.clone().requires_grad_(True)
+        self.alt_colors = d.colors.flip(0).contiguous() * 0.5
+        self.one_colors = torch.ones_like(d.colors)
         self.p = ([d.scales.clone().requires_grad_(True), d.rotation.clone().requires_grad_(True)] if param == "rs"
                   else [d.cholesky.clone().requires_grad_(True)])
 
@@ -121,6 +132,15 @@ class OurPipeline:
     def render(self):
         with torch.no_grad():
             return self.forward()
+
+    def model_forward(self):
+        s, d = self.s, self.d
+        with torch.no_grad():
+            if self.param == "rs":
+                pr = G.project_gaussians_2d_scale_rot(self.means, self.p[0], self.p[1], s.H, s.W, s.tile_bounds)
+            else:
+                pr = G.project_gaussians_2d(self.means, self.p[0], s.H, s.W, s.tile_bounds)
+            return [G.rasterize_gaussians_sum(*pr, k, d.opacity, s.H, s.W) for k in (self.colors, self.alt_colors, self.one_colors)]
 
     def fit(self):
         loss = torch.nn.functional.mse_loss(self.forward(), self.d.gt)
@@ -169,11 +189,17 @@ def main():
             continue
         R = RefPipeline(d, s, flavor, param)
         res[f"reference_cuda_{flavor}"] = {"render_fps": rate(R.render, reps), "fit_iters_per_s": rate(R.fit, reps),
+                                           "model_forward_per_s": rate(R.model_forward, reps),
                                            "flags": "-O3 --use_fast_math (pip build, setup.py:74-86)" if flavor == "fast"
                                            else "-O3 (JIT build, _backend.py:39-40)"}
     O = OurPipeline(d, s, param)
     ours = {"render_fps_eager_strict": rate(O.render, reps), "fit_iters_per_s_eager_strict": rate(O.fit, reps)}
+    ours["model_forward_per_s_eager_strict"] = rate(O.model_forward, reps)
+    G.set_memoise_binning(False)
+    ours["model_forward_per_s_eager_strict_no_memo"] = rate(O.model_forward, reps)
+    G.set_memoise_binning(True)
     G.set_sync_free(True)
+    ours["model_forward_per_s_graph"] = graph_rate(O.model_forward, reps)
     ours["render_fps_eager_sync_free"] = rate(O.render, reps)
     ours["fit_iters_per_s_eager_sync_free"] = rate(O.fit, reps)
     ours["render_fps_graph"] = graph_rate(O.render, reps)
@@ -188,6 +214,8 @@ def main():
             "render_graph": ours["render_fps_graph"] / ref["render_fps"],
             "fit_eager_strict": ours["fit_iters_per_s_eager_strict"] / ref["fit_iters_per_s"],
             "fit_graph": ours["fit_iters_per_s_graph"] / ref["fit_iters_per_s"],
+            "model_forward_eager_strict": ours["model_forward_per_s_eager_strict"] / ref["model_forward_per_s"],
+            "model_forward_graph": ours["model_forward_per_s_graph"] / ref["model_forward_per_s"],
         }
     txt = json.dumps(res, indent=1)
     print(txt)

@@ -525,3 +525,81 @@ def test_fused_chain_reports_overflow_and_does_not_write_out_of_bounds():
                                   _np(s.opacity), want_ambig=True)[3].astype(bool)
     assert_image_close(_np(out), want, "image after overflow retry", exclude=amb)
     assert RS._capacity[(torch.device(DEV).index, N, TX, TY)] > n_true
+
+
+# ------------------------------------------------------------------------------- memoised binning (Q13)
+def _model_forward(d, s, colors, opac):
+    """The reference model's forward (gaussianimage_cholesky.py:76-98): one projection, three rasterizations of the same
+    geometry -- the fitted colours, fixed 'visualisation' colours, and ones (the alpha map)."""
+    pr = G.project_gaussians_2d(d.means2d, d.cholesky, s.H, s.W, s.tile_bounds)
+    out = G.rasterize_gaussians_sum(*pr, colors, opac, s.H, s.W)
+    gauss = G.rasterize_gaussians_sum(*pr, d.colors.flip(0).contiguous() * 0.5, opac, s.H, s.W)
+    alpha = G.rasterize_gaussians_sum(*pr, torch.ones_like(colors), opac, s.H, s.W)
+    return pr, out, gauss, alpha
+
+
+@pytest.mark.parametrize("name", ["ragged", "c1_small", "dense"])
+@pytest.mark.parametrize("sync_free", [False, True])
+def test_three_renders_of_one_projection_reuse_the_binning_bit_for_bit(name, sync_free):
+    from gaussianimage_b200 import rasterize_sum as RS
+    s = scene(name)
+    d = s.to(DEV)
+    colors = d.colors.clone().requires_grad_(True)
+    opac = d.opacity.clone().requires_grad_(True)
+    G.set_sync_free(sync_free)
+    try:
+        G.set_memoise_binning(False)
+        _, w_out, w_gauss, w_alpha = _model_forward(d, s, colors, opac)
+        w_grads = torch.autograd.grad((w_out * d.gt).sum() + (w_alpha ** 2).sum(), [colors, opac])
+        G.set_memoise_binning(True)
+        h0 = RS.geometry_hits
+        pr, out, gauss, alpha = _model_forward(d, s, colors, opac)
+        assert RS.geometry_hits == h0 + 2
+        grads = torch.autograd.grad((out * d.gt).sum() + (alpha ** 2).sum(), [colors, opac])   # backward THROUGH a re-used list
+        for got, want in ((out, w_out), (gauss, w_gauss), (alpha, w_alpha)):
+            assert torch.equal(got, want)
+        for got, want in zip(grads, w_grads):
+            assert_grad_close(_np(got), _np(want), "gradient through a memoised render")
+        # the oracle agrees on the alpha map too (independent of the memoised path)
+        o_alpha, _ = O.render_cholesky(_np(s.means2d), _np(s.cholesky), np.ones_like(_np(s.colors)), _np(s.opacity), s.H, s.W,
+                                       want_all=True)
+        assert_image_close(_np(alpha), o_alpha, "alpha map vs oracle")
+        # an in-place change of the geometry invalidates the entry (version counter), a new projection too
+        h1 = RS.geometry_hits
+        pr[0].add_(0.25)
+        moved = G.rasterize_gaussians_sum(*pr, colors, opac, s.H, s.W)
+        assert RS.geometry_hits == h1
+        G.set_memoise_binning(False)
+        w_moved = G.rasterize_gaussians_sum(*pr, colors, opac, s.H, s.W)
+        assert torch.equal(moved, w_moved)
+        G.check_overflow(DEV)
+    finally:
+        G.set_memoise_binning(True)
+        G.set_sync_free(False)
+
+
+def test_model_forward_under_graph_capture_reuses_the_binning():
+    from gaussianimage_b200 import rasterize_sum as RS
+    s = scene("c1_small")
+    d = s.to(DEV)
+    colors, opac = d.colors.clone(), d.opacity.clone()
+    with torch.no_grad():
+        _, w_out, w_gauss, w_alpha = _model_forward(d, s, colors, opac)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            _model_forward(d, s, colors, opac)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        h0 = RS.geometry_hits
+        with torch.cuda.graph(g):
+            _, out, gauss, alpha = _model_forward(d, s, colors, opac)
+        assert RS.geometry_hits == h0 + 2
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, w_out) and torch.equal(gauss, w_gauss) and torch.equal(alpha, w_alpha)
+    # eager calls after the capture must not touch the captured entry
+    _, e_out, _, _ = _model_forward(d, s, colors, opac)
+    assert torch.equal(e_out, w_out)
