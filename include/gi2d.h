@@ -190,6 +190,33 @@ int gi2d_raster_sum_bwd(int N, int TX, int TY, int W, int H, const int *gids_sor
 int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
                                const float *v_out, float *grads12, cudaStream_t stream);
 
+/* ---- optimizer step -------------------------------------------------------------------------- */
+
+/* The Adan update of optimizer.py:232-279 (`_single_tensor_adan`; optimizer.py:296-362 is the same arithmetic as ~25
+ * torch._foreach launches) over all tensors of a parameter group in ONE launch (one per 16 tensors).  This is what the
+ * reference's own plug-in seam expects from the external module `fused_adan` (optimizer.py:365-449: adan_multi_tensor /
+ * adan_single_tensor; the CUDA extension of github.com/sail-sg/Adan, neither vendored nor pinned by the reference).
+ * numel / params / ... are HOST arrays of n_tensors entries (element counts; fp32 DEVICE pointers), all updated in place.
+ * The scalars are the ones the reference computes in Python doubles (optimizer.py:169-171, 210-214).  grads are scaled
+ * by clip_global_grad_norm in place when it is not 1 (as optimizer.py:240 does).  update_neg_pre_grad != 0 also stores
+ * neg_pre_grad = -grad (optimizer.py:268, :394-395), which the reference's fused wrapper does with two more launches. */
+int gi2d_adan_multi_tensor(int n_tensors, const long long *numel, void *const *params, void *const *grads,
+                           void *const *exp_avgs, void *const *exp_avg_sqs, void *const *exp_avg_diffs,
+                           void *const *neg_pre_grads, double beta1, double beta2, double beta3, double bias_correction1,
+                           double bias_correction2, double bias_correction3_sqrt, double lr, double weight_decay, double eps,
+                           int no_prox, double clip_global_grad_norm, int update_neg_pre_grad, cudaStream_t stream);
+
+/* CUDA-graph-capturable form: hyper-parameters and the step counter live in a DEVICE block of gi2d_adan_state_bytes()
+ * bytes (fill a host copy with gi2d_adan_state_init and upload it; re-upload when lr changes).  The kernel derives the
+ * bias corrections of step+1 in double and the last block to finish advances the counter, so replaying the same graph
+ * performs successive optimizer steps.  At most 16 tensors per call. */
+size_t gi2d_adan_state_bytes(void);
+int gi2d_adan_state_init(void *state_host, double beta1, double beta2, double beta3, double lr, double weight_decay, double eps,
+                         double clip_global_grad_norm, int step);
+int gi2d_adan_multi_tensor_graph(int n_tensors, const long long *numel, void *const *params, void *const *grads,
+                                 void *const *exp_avgs, void *const *exp_avg_sqs, void *const *exp_avg_diffs,
+                                 void *const *neg_pre_grads, void *state_dev, int no_prox, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
