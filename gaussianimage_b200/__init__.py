@@ -6,6 +6,7 @@ all over the C ABI of libgi2d.so (include/gi2d.h).  `import gsplat` (the alias p
 resolves to these modules so that the reference's gaussianimage_cholesky.py / gaussianimage_rs.py / train.py /
 test_quantize.py run unchanged.  There is no CPU fallback.
 """
+from .decode import decode_project_gaussians_2d
 from .project_gaussians_2d import project_gaussians_2d
 from .project_gaussians_2d_scale_rot import project_gaussians_2d_scale_rot
 from .rasterize_sum import check_overflow, rasterize_gaussians_sum, set_memoise_binning, set_sync_free
@@ -32,4 +33,5 @@ __all__ = [
     "set_sync_free",
     "check_overflow",
     "set_memoise_binning",
+    "decode_project_gaussians_2d",
 ]

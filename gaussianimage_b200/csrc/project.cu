@@ -10,6 +10,8 @@
 // 3-float rows as 192 coalesced 16-byte vectors through shared memory (rows start at 256*12 B = 3072 B multiples),
 // so global traffic is full 128-B lines in both directions; the per-thread reads of shared memory are stride-3 words,
 // which is bank-conflict free.
+#include <cuda_fp16.h>
+
 #include "gi2d_common.cuh"
 
 namespace gi2d {
@@ -223,6 +225,74 @@ static inline int cuda_status() {
     return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Codec decode prologue fused into the Cholesky projection: what decompress_wo_ec does with torch ops
+// before every decode render (gaussianimage_cholesky.py:161-166) --
+//     means    = tanh(xyz.float())                                   fp16 positions
+//     cholesky = codes * scale + beta + cholesky_bound               UniformQuantizer.decompress (quantize.py:86-87)
+//     colors   = sum_k codebook_k[index[:, k]]                       VectorQuantizer.decompress (quantize.py:146-150)
+// -- and project_gaussians_2d, in one pass: 4+3(+12)+8K B in, 32+12 B out per Gaussian instead of seven kernels that
+// write and re-read means / cholesky / colours.  Roundings follow the torch ops one by one (mul, add, add; 0 + a + b).
+template <bool CODE_F32, bool IDX64>
+__global__ void __launch_bounds__(PB) decode_project_kernel(int N, const __half2 *__restrict__ xyz, const void *__restrict__ codes,
+                                                            const float *__restrict__ scale3, const float *__restrict__ beta3,
+                                                            const float *__restrict__ bound3, const void *__restrict__ index,
+                                                            int K, int C, const float *__restrict__ codebooks, float hw, float hh,
+                                                            int TX, int TY, float *__restrict__ xys, float *__restrict__ depths,
+                                                            int *__restrict__ radii, float *__restrict__ conics,
+                                                            int *__restrict__ num_tiles_hit, float *__restrict__ colors) {
+    extern __shared__ __align__(16) float s_cb[];      // K*C*3 codebook floats (when they fit), then 3*PB staging floats
+    const int ncb = K * C * 3;
+    float *s3 = s_cb + ((ncb + 3) & ~3);
+    const int base = blockIdx.x * PB, tid = threadIdx.x, i = base + tid;
+    const int nb = min(PB, N - base);
+    for (int k = tid; k < ncb; k += PB) s_cb[k] = __ldg(codebooks + k);
+    __syncthreads();
+    float2 xy = make_float2(0.f, 0.f);
+    float3 conic = make_float3(0.f, 0.f, 0.f), col = make_float3(0.f, 0.f, 0.f);
+    int radius = 0, tiles = 0;
+    if (i < N) {
+        const float2 z = __half22float2(xyz[i]);
+        const float mx = tanhf(z.x), my = tanhf(z.y);            // gaussianimage_cholesky.py:163 (libdevice tanhf, as torch)
+        float q0, q1, q2;
+        if (CODE_F32) {
+            const float *c = reinterpret_cast<const float *>(codes) + 3 * (size_t)i;
+            q0 = __ldg(c); q1 = __ldg(c + 1); q2 = __ldg(c + 2);
+        } else {
+            const uint8_t *c = reinterpret_cast<const uint8_t *>(codes) + 3 * (size_t)i;
+            q0 = (float)__ldg(c); q1 = (float)__ldg(c + 1); q2 = (float)__ldg(c + 2);
+        }
+        const float3 scale = make_float3(__ldg(scale3), __ldg(scale3 + 1), __ldg(scale3 + 2));
+        const float3 beta = make_float3(__ldg(beta3), __ldg(beta3 + 1), __ldg(beta3 + 2));
+        const float3 bound = make_float3(__ldg(bound3), __ldg(bound3 + 1), __ldg(bound3 + 2));
+        const float l11 = __fadd_rn(__fadd_rn(__fmul_rn(q0, scale.x), beta.x), bound.x);    // quantize.py:87, then :165
+        const float l21 = __fadd_rn(__fadd_rn(__fmul_rn(q1, scale.y), beta.y), bound.y);
+        const float l22 = __fadd_rn(__fadd_rn(__fmul_rn(q2, scale.z), beta.z), bound.z);
+        for (int k = 0; k < K; ++k) {                            // quantize.py:147-149: recon = 0; recon += embed[0, index[:, k]]
+            long long e = IDX64 ? __ldg(reinterpret_cast<const long long *>(index) + (size_t)i * K + k)
+                                : (long long)__ldg(reinterpret_cast<const int *>(index) + (size_t)i * K + k);
+            e = e < 0 ? 0 : (e >= C ? C - 1 : e);               // torch would raise; never read outside the codebook
+            const float *row = s_cb + ((size_t)k * C + (size_t)e) * 3;
+            col.x = __fadd_rn(col.x, row[0]); col.y = __fadd_rn(col.y, row[1]); col.z = __fadd_rn(col.z, row[2]);
+        }
+        const float cx = ffma(hw, mx, hw);
+        const float cy = ffma(my, hh, hh);
+        const float a = fmul(l11, l11), b = fmul(l11, l21), c = ffma(l21, l21, fmul(l22, l22));
+        project_tail(cx, cy, a, b, c, TX, TY, xy, radius, conic, tiles);
+        reinterpret_cast<float2 *>(xys)[i] = xy;
+        depths[i] = 0.f;
+        radii[i] = radius;
+        num_tiles_hit[i] = tiles;
+    }
+    s3[3 * tid] = conic.x; s3[3 * tid + 1] = conic.y; s3[3 * tid + 2] = conic.z;
+    __syncthreads();
+    stage_out3<true>(s3, conics, base, nb);
+    __syncthreads();
+    s3[3 * tid] = col.x; s3[3 * tid + 1] = col.y; s3[3 * tid + 2] = col.z;
+    __syncthreads();
+    stage_out3<true>(s3, colors, base, nb);
+}
+
 }  // namespace gi2d
 
 using namespace gi2d;
@@ -318,6 +388,33 @@ int gi2d_project_scale_rot_bwd_packed(int N, const float *scales2d, const float 
         project_bwd_kernel<1, true><<<grid, PB, 0, stream>>>(N, nullptr, scales2d, rotation, hw, hh, radii, conics, nullptr, nullptr, nullptr, v_mean2d, nullptr, v_scale, v_rot, g);
     else
         project_bwd_kernel<1, false><<<grid, PB, 0, stream>>>(N, nullptr, scales2d, rotation, hw, hh, radii, conics, nullptr, nullptr, nullptr, v_mean2d, nullptr, v_scale, v_rot, g);
+    return cuda_status();
+}
+
+int gi2d_decode_project_cholesky_fwd(int N, const void *xyz_half, const void *codes, int codes_are_f32, const float *scale3,
+                                     const float *beta3, const float *bound3, const void *index, int index_is_i64,
+                                     int n_quantizers, int codebook_size, const float *codebooks, int H, int W, int TX, int TY,
+                                     float *xys, float *depths, int *radii, float *conics, int *num_tiles_hit, float *colors,
+                                     cudaStream_t stream) {
+    if (N < 0 || H <= 0 || W <= 0 || n_quantizers < 0 || codebook_size <= 0 || !scale3 || !beta3 || !bound3) return GI2D_ERR_INVALID;
+    if (N == 0) return GI2D_OK;
+    if (!xyz_half || !codes || (n_quantizers && (!index || !codebooks))) return GI2D_ERR_INVALID;
+    if (!aligned16(xys) || !aligned16(conics) || !aligned16(colors) || (reinterpret_cast<uintptr_t>(xyz_half) & 3)) return GI2D_ERR_INVALID;
+    const size_t ncb = (size_t)n_quantizers * codebook_size * 3;
+    const size_t smem = (((ncb + 3) & ~(size_t)3) + 3 * PB) * sizeof(float);
+    if (smem > 200 * 1024) return GI2D_ERR_INVALID;           // codebooks of the codec are 2 x 8 x 3 floats
+    const float hw = (float)(unsigned)W * 0.5f, hh = (float)(unsigned)H * 0.5f;
+    const int grid = (N + PB - 1) / PB;
+#define GI2D_DECODE(F, I)                                                                                                 \
+    {                                                                                                                     \
+        if (smem > 48 * 1024) cudaFuncSetAttribute(decode_project_kernel<F, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        decode_project_kernel<F, I><<<grid, PB, smem, stream>>>(N, reinterpret_cast<const __half2 *>(xyz_half), codes, scale3, beta3, bound3, index, \
+                                                                n_quantizers, codebook_size, codebooks, hw, hh, TX, TY, xys, depths, \
+                                                                radii, conics, num_tiles_hit, colors);                   \
+    }
+    if (codes_are_f32) { if (index_is_i64) GI2D_DECODE(true, true) else GI2D_DECODE(true, false) }
+    else { if (index_is_i64) GI2D_DECODE(false, true) else GI2D_DECODE(false, false) }
+#undef GI2D_DECODE
     return cuda_status();
 }
 

@@ -121,6 +121,17 @@ class RowShardedRenderer:
             dist.all_gather_into_tensor(self.buffer, mine, group=self.group)
         return self.frame()
 
+    def render_compressed(self, xyz, quant_cholesky_elements, scale, beta, cholesky_bound, feature_dc_index, codebooks,
+                          opacity) -> torch.Tensor:
+        """decode step from the compressed representation (compress_wo_ec, gaussianimage_cholesky.py:154-159): the
+        de-quantisation prologue and the projection are ONE kernel (decode.py), then own band, then the exchange."""
+        from .decode import decode_project_gaussians_2d
+        xys, depths, radii, conics, nth, colors = decode_project_gaussians_2d(
+            xyz, quant_cholesky_elements, scale, beta, cholesky_bound, feature_dc_index, codebooks, self.H, self.W,
+            (self.TX, self.TY, 1))
+        self.render_band(xys, radii, conics, nth, colors, opacity)
+        return self.gather()
+
     def render(self, means2d, L_elements, colors, opacity) -> torch.Tensor:
         """decode step: project all Gaussians (every rank), render own band, all-gather -> (H,W,3) frame."""
         N = means2d.shape[0]

@@ -48,6 +48,20 @@ const char *gi2d_status_string(int status);
 int gi2d_project_cholesky_fwd(int N, const float *means2d, const float *L, int H, int W, int TX, int TY, float *xys,
                               float *depths, int *radii, float *conics, int *num_tiles_hit, cudaStream_t stream);
 
+/* Codec decode prologue fused into the Cholesky projection.  Replaces, for decompress_wo_ec / decompress
+ * (gaussianimage_cholesky.py:161-166, :214-218), the torch ops
+ *     means = tanh(xyz.float());  cholesky = codes * scale + beta (quantize.py:86-87) + cholesky_bound;
+ *     colors = sum_k codebook_k[index[:, k]] (quantize.py:146-150)
+ * and the project_gaussians_2d call that follows.  xyz_half (N,2) fp16; codes (N,3) uint8 or fp32 (codes_are_f32);
+ * scale3 / beta3 / bound3: 3 fp32 each (DEVICE); index (N,n_quantizers) int32 or int64 (index_is_i64), values in
+ * [0, codebook_size) (clamped into range, where torch would raise); codebooks (n_quantizers, codebook_size, 3) fp32.
+ * Outputs as gi2d_project_cholesky_fwd plus colors (N,3).  xys / conics / colors must be 16-byte aligned. */
+int gi2d_decode_project_cholesky_fwd(int N, const void *xyz_half, const void *codes, int codes_are_f32, const float *scale3,
+                                     const float *beta3, const float *bound3, const void *index, int index_is_i64,
+                                     int n_quantizers, int codebook_size, const float *codebooks, int H, int W, int TX, int TY,
+                                     float *xys, float *depths, int *radii, float *conics, int *num_tiles_hit, float *colors,
+                                     cudaStream_t stream);
+
 /* Replaces project_gaussians_2d_scale_rot_forward (ext.cpp:18 -> bindings.cu:841-899 -> foward2d.cu:71-123).
  * scales2d (N,2), rotation (N,1) radians. */
 int gi2d_project_scale_rot_fwd(int N, const float *means2d, const float *scales2d, const float *rotation, int H, int W,
