@@ -764,7 +764,7 @@ static bool all_resident_smem(K kernel, int threads, size_t smem, int grid) {
 }
 
 struct FusedLayout {          // carve-up of the caller's workspace for gi2d_bin_fused
-    size_t ctl, scan_state, lookback, zero_bytes, keys_a, keys_b, vals_b, mat, total;
+    size_t ctl, tile_state, tile_cur, zero_scatter, scan_state, lookback, zero_bytes, keys_a, keys_b, vals_b, mat, total;
     int scan_blocks, sort_blocks, npass;
 };
 static FusedLayout fused_layout(int N, int T, int capacity) {
@@ -774,6 +774,9 @@ static FusedLayout fused_layout(int N, int T, int capacity) {
     L.sort_blocks = (capacity + MIN_SORT_TILE - 1) / MIN_SORT_TILE;
     size_t o = 0;
     L.ctl = o; o += align_up(sizeof(uint32_t) * CTL_WORDS, 256);
+    L.tile_state = o; o += align_up(sizeof(uint32_t) * (size_t)((T + 1023) / 1024 + 1), 256);   // scatter path: look-back words
+    L.tile_cur = o; o += align_up(sizeof(uint32_t) * (size_t)T, 256);                            // scatter path: per-tile counters
+    L.zero_scatter = o;
     L.scan_state = o; o += align_up(sizeof(uint32_t) * (size_t)L.scan_blocks, 256);
     L.lookback = o; o += align_up(sizeof(uint32_t) * (size_t)L.npass * L.sort_blocks * RADIX, 256);
     L.zero_bytes = o;
@@ -821,6 +824,165 @@ static SmallPlan small_plan(int N, int T) {
 #undef GI2D_TRY
     }
     return p;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Scatter path for images of MORE than 4096 tiles (the 8K decode: 129 600 tiles, 19 intersections per tile on average).
+// A radix sort of the (tile, gid) pairs moves every pair once per 8 tile-id bits and is latency-bound at these sizes
+// (C5: scan 61 us + 3 passes = 253 us).  Tiles are small, so bin by tile with atomics instead and repair the order
+// inside each tile:
+//   K1 tile_count    every (Gaussian, tile) pair adds 1 to its tile's counter (RED.ADD, no return value);
+//   K2 tile_scan     exclusive scan of the counters in place (single pass, decoupled look-back) = first slot of every
+//                    tile; the total goes to status / the mapped host word;
+//   K3 tile_scatter  every pair takes slot = atomicAdd(cursor[tile], 1) and stores its gid there -- any order inside
+//                    the tile; afterwards cursor[tile] is the END of the tile;
+//   K4 tile_sort_pack  one warp per tile sorts the tile's gids ascending (a Gaussian hits a tile at most once, so the
+//                    order is total and equals the reference's stable sort, Q2): <= 32 by shuffle ranking, <= 512 by a
+//                    bitonic network in shared memory, longer in place in global memory; then writes tile_bins and the
+//                    48-byte packed records.
+// Deterministic output although the scatter is not.  Slots >= capacity are never written (overflow is reported).
+struct ScatterArgs {
+    int N, TX, TY, T, capacity, wy0, wy1;
+    const float *xys;
+    const int *radii, *nth;
+    const float *conics, *colors, *opac;
+    uint32_t *cur;            // (T): counters -> exclusive starts -> ends
+    uint32_t *scan_state, *ctl;
+    int *gids_sorted, *tile_bins;
+    float4 *packed;
+    int *status_out;
+    volatile int *status_host;
+};
+
+__device__ __forceinline__ void scatter_rect(const ScatterArgs &a, int i, int &cnt, int &x0, int &w, int &y0) {
+    cnt = 0; x0 = 0; w = 1; y0 = 0;
+    if (i >= a.N) return;
+    const int nth = __ldg(a.nth + i);
+    if (nth <= 0) return;
+    int area;
+    gaussian_bbox(a.xys, a.radii, i, a.TX, a.TY, x0, w, y0, area, a.wy0, a.wy1);
+    const bool windowed = a.wy0 > 0 || a.wy1 < a.TY;
+    cnt = windowed ? area : min(nth, area);        // the projections always give num_tiles_hit == area
+}
+
+template <bool SCATTER>
+__global__ void __launch_bounds__(256) tile_count_scatter_kernel(ScatterArgs a) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    int cnt, x0, w, y0;
+    scatter_rect(a, i, cnt, x0, w, y0);
+    warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int gid, int, bool active) {
+        if (!active) return;
+        if (!SCATTER) {
+            atomicAdd(a.cur + tile, 1u);
+        } else {
+            const uint32_t pos = atomicAdd(a.cur + tile, 1u);
+            if (pos < (uint32_t)a.capacity) a.gids_sorted[pos] = gid;
+        }
+    });
+}
+
+template <int NT>
+__global__ void __launch_bounds__(NT) tile_scan_kernel(ScatterArgs a, int use_ticket) {
+    __shared__ int s_warp[NT / 32];
+    __shared__ int s_bcast[2];
+    const int tid = threadIdx.x;
+    if (use_ticket && tid == 0) s_bcast[0] = (int)atomicAdd(a.ctl + CTL_SCAN_TICKET, 1u);
+    __syncthreads();
+    const int vbid = use_ticket ? s_bcast[0] : (int)blockIdx.x;
+    const int t = vbid * NT + tid;
+    const int c = t < a.T ? (int)a.cur[t] : 0;
+    int block_total;
+    const int incl = block_incl_scan<NT>(c, s_warp, &block_total);
+    if (tid < 32) {
+        const int e = lookback_exclusive(a.scan_state, vbid, block_total);
+        if (tid == 0) s_bcast[1] = e;
+    }
+    __syncthreads();
+    const int excl = s_bcast[1] + incl - c;
+    if (t < a.T) a.cur[t] = (uint32_t)excl;
+    if (vbid == (int)gridDim.x - 1 && tid == 0) {
+        const int total = s_bcast[1] + block_total;
+        const int over = total > a.capacity ? 1 : 0;
+        a.ctl[CTL_N] = (uint32_t)total;
+        a.ctl[CTL_OVERFLOW] = (uint32_t)over;
+        if (a.status_out) { a.status_out[0] = total; a.status_out[1] = over; }
+        if (a.status_host) {
+            a.status_host[1] = over;
+            __threadfence_system();
+            a.status_host[0] = total;
+        }
+    }
+}
+
+// Ascending in-place sort of buf[0, L) by one warp: bitonic network in its all-merges-ascending form (first step of a
+// merge pairs i with i ^ (k - 1)), so virtual +inf padding beyond L never has to move.  buf may be shared or global.
+__device__ __forceinline__ void warp_bitonic(int *buf, int L) {
+    const int lane = threadIdx.x & 31;
+    int P = 64;
+    while (P < L) P <<= 1;
+    for (int k = 2; k <= P; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const bool flip = j == (k >> 1);
+            for (int i = lane; i < P; i += 32) {
+                const int l = flip ? (i ^ (k - 1)) : (i ^ j);
+                if (l > i && l < L) {
+                    const int x = buf[i], y = buf[l];
+                    if (x > y) { buf[i] = y; buf[l] = x; }
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+constexpr int SORT_SMEM = 512;     // gids per warp sorted in shared memory
+
+__global__ void __launch_bounds__(256) tile_sort_pack_kernel(ScatterArgs a) {
+    __shared__ int s_buf[8][SORT_SMEM];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile = blockIdx.x * 8 + warp;
+    if (tile >= a.T) return;
+    const int cap = a.capacity;
+    const int lo = min(tile ? (int)min(a.cur[tile - 1], (uint32_t)0x7fffffff) : 0, cap);
+    const int hi = min((int)min(a.cur[tile], (uint32_t)0x7fffffff), cap);
+    const int L = hi - lo;
+    if (lane == 0) reinterpret_cast<int2 *>(a.tile_bins)[tile] = L > 0 ? make_int2(lo, hi) : make_int2(0, 0);
+    if (L <= 0) return;
+    int *g = a.gids_sorted + lo;
+    auto put_record = [&](int slot, int v) {
+        const size_t q = (size_t)v;
+        const float x = __ldg(a.xys + 2 * q), y = __ldg(a.xys + 2 * q + 1);
+        const float cx = __ldg(a.conics + 3 * q), cy = __ldg(a.conics + 3 * q + 1), cz = __ldg(a.conics + 3 * q + 2);
+        const float r = __ldg(a.colors + 3 * q), gg = __ldg(a.colors + 3 * q + 1), b = __ldg(a.colors + 3 * q + 2);
+        const float o = __ldg(a.opac + q);
+        float4 *dst = a.packed + 3 * (size_t)(lo + slot);
+        __stcs(dst + 0, make_float4(x, y, o, cx));
+        __stcs(dst + 1, make_float4(cy, cz, r, gg));
+        __stcs(dst + 2, make_float4(b, __int_as_float(v), 0.f, 0.f));
+    };
+    if (L <= 32) {                                  // one gid per lane: its rank is its slot, nothing is re-read
+        const int v = lane < L ? g[lane] : 0x7fffffff;
+        int rank = 0;
+        for (int k = 0; k < L; ++k) rank += __shfl_sync(0xffffffffu, v, k) < v;
+        if (lane < L) {
+            g[rank] = v;
+            put_record(rank, v);
+        }
+        return;
+    }
+    const int *src = g;
+    if (L <= SORT_SMEM) {
+        for (int k = lane; k < L; k += 32) s_buf[warp][k] = g[k];
+        __syncwarp();
+        warp_bitonic(s_buf[warp], L);
+        for (int k = lane; k < L; k += 32) g[k] = s_buf[warp][k];
+        src = s_buf[warp];
+    } else {
+        __syncwarp();
+        warp_bitonic(g, L);                          // rare: a tile with more than 512 intersections
+    }
+    __syncwarp();
+    for (int k = lane; k < L; k += 32) put_record(k, src[k]);
 }
 
 // Records of an EXISTING sorted list with other per-Gaussian attributes: a caller that renders the same geometry several
@@ -950,10 +1112,17 @@ int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *ti
 
 // Number of kernels gi2d_bin_fused launches for this shape on the current device (1 = the one-kernel path; otherwise the
 // scan kernel + one onesweep pass per 8 tile-id bits); the zero-fill of the chain's control block is a memset, not a kernel.
+// GI2D_SCATTER_BIN: 0 = never, 1 (default) = images of more than 4096 tiles, 2 = whenever the one-kernel path does not apply
+static bool use_scatter(int T) {
+    static const int mode = env_int("GI2D_SCATTER_BIN", 1);
+    return mode == 2 || (mode == 1 && T > 4096);
+}
+
 int gi2d_bin_fused_kernel_count(int N, int TX, int TY) {
     if (N <= 0 || TX <= 0 || TY <= 0) return 0;
     const int T = TX * TY;
     if (small_plan(N, T).fn) return 1;
+    if (use_scatter(T)) return 4;
     return 1 + make_plan(0, ceil_log2(T > 1 ? T : 2)).npass;
 }
 
@@ -998,6 +1167,19 @@ int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, 
             const cudaError_t e = cudaLaunchCooperativeKernel(sp.fn, dim3((N + sp.nt - 1) / sp.nt), dim3(sp.nt), args, sp.smem, stream);
             return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
         }
+    }
+
+    if (use_scatter(T)) {          // count -> scan -> scatter -> per-tile sort + records
+        cudaMemsetAsync(ws, 0, L.zero_scatter, stream);
+        ScatterArgs a{N, TX, TY, T, capacity, ty_begin, ty_end, xys, radii, num_tiles_hit, conics, colors, opacities,
+                      reinterpret_cast<uint32_t *>(base + L.tile_cur), reinterpret_cast<uint32_t *>(base + L.tile_state), ctl,
+                      gids_sorted, tile_bins, reinterpret_cast<float4 *>(packed), status_out, status_host};
+        const int gblocks = (N + 255) / 256, sblocks = (T + 1023) / 1024;
+        tile_count_scatter_kernel<false><<<gblocks, 256, 0, stream>>>(a);
+        tile_scan_kernel<1024><<<sblocks, 1024, 0, stream>>>(a, all_resident(tile_scan_kernel<1024>, 1024, sblocks) ? 0 : 1);
+        tile_count_scatter_kernel<true><<<gblocks, 256, 0, stream>>>(a);
+        tile_sort_pack_kernel<<<(T + 7) / 8, 256, 0, stream>>>(a);
+        return cuda_status();
     }
 
     cudaMemsetAsync(ws, 0, L.zero_bytes, stream);

@@ -478,16 +478,19 @@ def test_row_sharded_bands_reproduce_the_single_gpu_frame_bit_for_bit(world):
 
 
 # ------------------------------------------------------------------------------------------------ binning variants
-@pytest.mark.parametrize("env", [{"GI2D_SMALL_BIN": "0"}, {"GI2D_SMALL_NT": "256"}, {"GI2D_SMALL_NT": "1024"}],
-                         ids=["onesweep_chain", "one_kernel_nt256", "one_kernel_nt1024"])
+@pytest.mark.parametrize("env", [{"GI2D_SMALL_BIN": "0", "GI2D_SCATTER_BIN": "0"}, {"GI2D_SMALL_NT": "256"}, {"GI2D_SMALL_NT": "1024"},
+                                 {"GI2D_SMALL_BIN": "0", "GI2D_SCATTER_BIN": "2"}],
+                         ids=["onesweep_chain", "one_kernel_nt256", "one_kernel_nt1024", "scatter_path"])
 def test_every_binning_path_passes_the_list_and_image_checks(env):
-    """The fused chain has two implementations (one cooperative counting-sort kernel for <= 4096 tiles with three block
-    shapes; scan + onesweep passes otherwise), chosen inside the library.  The choice is read from the environment once
+    """The fused chain has three implementations (one cooperative counting-sort kernel for <= 4096 tiles with three block
+    shapes; count / scan / scatter / per-tile sort for more tiles; scan + onesweep passes as the general fallback), chosen
+    inside the library.  The choice is read from the environment once
     per process, so each variant re-runs the list / image / fit-step parity tests in a fresh interpreter."""
     import os
     import subprocess
     import sys
-    sel = "fused_chain_lists or forward_bit_exact or operator_fit_step or zero_intersections or backward_vs_oracle"
+    sel = ("fused_chain_lists or forward_bit_exact or operator_fit_step or zero_intersections or backward_vs_oracle or "
+           "fused_chain_reports_overflow or row_sharded_bands or full_size_properties")
     r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_gpu_parity.py", "-q", "-x", "-m", "gpu", "-k", sel,
                         "-p", "no:cacheprovider"], env={**os.environ, **env}, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
