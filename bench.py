@@ -198,8 +198,22 @@ class FitStep:
         grads = torch.autograd.grad(loss, [self.means, *self.p, self.colors])
         return loss, grads
 
-    def capture(self, render_only=False):
+    def eager_fused_loss(self):
+        """The same step with the loss epilogue inside the rasterizer (gaussianimage_b200/loss.py)."""
         import torch
+        import gaussianimage_b200 as G
+        s = self.s
+        if self.param == "rs":
+            proj = G.project_gaussians_2d_scale_rot(self.means, self.p[0], self.p[1], s.H, s.W, s.tile_bounds)
+        else:
+            proj = G.project_gaussians_2d(self.means, self.p[0], s.H, s.W, s.tile_bounds)
+        loss = G.rasterize_gaussians_sum_mse(*proj, self.colors, self.opacity, s.H, s.W, self.gt, clamp=False, background=self.bg)
+        return loss, torch.autograd.grad(loss, [self.means, *self.p, self.colors])
+
+    def capture(self, render_only=False, fused_loss=False):
+        import torch
+        if fused_loss:
+            self.eager = self.eager_fused_loss
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):               # eager warm-up: learns the intersection capacity (strict mode)
@@ -377,6 +391,20 @@ def run_b200(args):
     torch.cuda.synchronize()
     warm_ms = a.elapsed_time(b) / K
 
+    # the same step with the MSE loss fused into the rasterizer's epilogue (informational: callers must opt in)
+    fused_ms = None
+    if not render_only:
+        fstep = FitStep(d, scene_cpu, param)
+        fstep.capture(fused_loss=True)
+        fstep.graph.replay()
+        if abs(fstep.loss.item() - step.loss.item()) > 1e-5 * abs(step.loss.item()):
+            raise RuntimeError(f"fused-loss step disagrees with the reference-API step: {fstep.loss.item()} vs {step.loss.item()}")
+        for _ in range(Wm):
+            fstep.graph.replay()
+        barrier()
+        fused_ms = sum(timed_replays(fstep.graph.replay, K, flush)) / K
+        G.check_overflow(dev)
+
     # ---- e2e: the step's inputs come from pinned host memory EVERY step (H2D inside the timed region) and its result is
     # read back to the host EVERY step (D2H).  Two-deep software pipeline: the H2D copy of step i+1 runs on a copy stream
     # while step i computes, and the host reads step i's result while step i+1 is in flight; the serial variant
@@ -525,7 +553,8 @@ def run_b200(args):
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
         "roofline": roof, "stages": table, "cpu_baseline": cpu,
         "extras": {"warm_l2_back_to_back_ms_per_step": warm_ms, "warm_l2_iters_per_s": 1e3 / warm_ms,
-                   "n_isect_checked": n_isect},
+                   "n_isect_checked": n_isect,
+                   "fused_loss_epilogue_ms_per_step": fused_ms, "fused_loss_epilogue_iters_per_s": (1e3 / fused_ms) if fused_ms else None},
     }
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -7,6 +7,7 @@ resolves to these modules so that the reference's gaussianimage_cholesky.py / ga
 test_quantize.py run unchanged.  There is no CPU fallback.
 """
 from .decode import decode_project_gaussians_2d
+from .loss import rasterize_gaussians_sum_mse
 from .project_gaussians_2d import project_gaussians_2d
 from .project_gaussians_2d_scale_rot import project_gaussians_2d_scale_rot
 from .rasterize_sum import check_overflow, rasterize_gaussians_sum, set_memoise_binning, set_sync_free
@@ -34,4 +35,5 @@ __all__ = [
     "check_overflow",
     "set_memoise_binning",
     "decode_project_gaussians_2d",
+    "rasterize_gaussians_sum_mse",
 ]

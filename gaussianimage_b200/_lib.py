@@ -39,6 +39,9 @@ _SIGNATURES = {
     "gi2d_adan_state_bytes": (_sz, []),
     "gi2d_adan_state_init": (_i, [_vp] + [C.c_double] * 7 + [_i]),
     "gi2d_adan_multi_tensor_graph": (_i, [_i] + [_vp] * 7 + [_vp, _i, _vp]),
+    "gi2d_raster_mse_workspace_bytes": (_sz, []),
+    "gi2d_raster_sum_fwd_packed_mse": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gi2d_raster_sum_bwd_packed_scaled": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_repack_records": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_bin_fused": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_bin_fused_rows": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),

@@ -90,13 +90,29 @@ __device__ __forceinline__ void multimem_st(float *mc, float v) {
 // k+1's records is already in flight into the other stage (its tile_bins range was fetched one tile earlier still).
 // At 8K (130k sparse tiles) the per-tile chain  range load -> TMA -> evaluate -> store  is latency-bound; the
 // two-deep prefetch takes the first two links off the critical path.
-template <bool TMA, bool AUX>
+// Loss epilogue: with LOSS the kernel does not write the image; per pixel it forms what the caller would
+// compute next --  image = clamp(out_img, 0, 1)  (gaussianimage_cholesky.py:84),  F.mse_loss(image, gt)  (utils.py:20-25) --
+// and writes the gradient of that loss w.r.t. out_img,  v_out = 2/(3HW) (image - gt) [0 <= out_img <= 1],  straight into the
+// buffer the backward rasterizer reads.  The squared error is summed per thread over the CTA's tiles, reduced once per
+// CTA, and the last CTA to finish adds the per-CTA partials in index order: a deterministic loss, no atomics on floats.
+struct LossArgs {
+    const float *gt;          // target, (3,H,W) planes when gt_chw else (H,W,3)
+    int gt_chw, clamp;
+    float inv_numel;          // 1 / (3 H W)
+    float *v_out;             // (H,W,3): d loss / d out_img
+    float *image;             // optional (H,W,3): the clamped image
+    float *partials;          // (gridDim.x)
+    unsigned int *ticket;     // zero before the launch; reset by the kernel
+    float *loss;              // (1)
+};
+
+template <bool TMA, bool AUX, bool LOSS = false>
 __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int n_tiles, int *tile_bins,
                                                         const float4 *__restrict__ packed, GatherSrc src,
                                                         const int *__restrict__ d_status,
                                                         const float *__restrict__ background, float *__restrict__ out_img,
                                                         float *__restrict__ final_Ts, int *__restrict__ final_idx,
-                                                        float *out_mc, int vec_ok) {
+                                                        float *out_mc, int vec_ok, LossArgs la = LossArgs{}) {
     constexpr int NSTAGE = TMA ? 2 : 1;
     __shared__ __align__(128) float4 s_rec[NSTAGE][RB * 3];
     __shared__ __align__(8) uint64_t s_bar[NSTAGE];
@@ -140,6 +156,7 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
         }
     }
     uint32_t phase_bits = 0;                              // bit st = parity of the next completion of s_bar[st]
+    float sq_sum = 0.f;                                   // LOSS: this thread's share of the squared error
 
     for (int it = 0; k < n_tiles; k += stride, ++it) {
         const int st = TMA ? (it & 1) : 0;
@@ -217,6 +234,27 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
         // staged through shared memory; with `out_mc` (the NVLS multicast alias of a symmetric frame buffer) every store
         // is a `multimem.st`, which the NVSwitch replicates into the frame buffer of EVERY rank -- the all-gather of a
         // row-sharded render happens inside the rasterizer.
+        if (LOSS) {
+            float cr = r, cg = g, cb = b;
+            if (la.clamp) { cr = fminf(fmaxf(r, 0.f), 1.f); cg = fminf(fmaxf(g, 0.f), 1.f); cb = fminf(fmaxf(b, 0.f), 1.f); }
+            float dr = 0.f, dg = 0.f, db = 0.f;
+            if (inside) {
+                if (la.gt_chw) {
+                    const size_t plane = (size_t)H * W;
+                    dr = cr - __ldg(la.gt + pix); dg = cg - __ldg(la.gt + plane + pix); db = cb - __ldg(la.gt + 2 * plane + pix);
+                } else {
+                    dr = cr - __ldg(la.gt + 3 * pix); dg = cg - __ldg(la.gt + 3 * pix + 1); db = cb - __ldg(la.gt + 3 * pix + 2);
+                }
+                sq_sum += dr * dr + dg * dg + db * db;
+                if (la.image) { la.image[3 * pix] = cr; la.image[3 * pix + 1] = cg; la.image[3 * pix + 2] = cb; }
+            }
+            const float sc = 2.f * la.inv_numel;
+            // torch.clamp passes the gradient where min <= x <= max
+            r = (!la.clamp || (r >= 0.f && r <= 1.f)) ? sc * dr : 0.f;
+            g = (!la.clamp || (g >= 0.f && g <= 1.f)) ? sc * dg : 0.f;
+            b = (!la.clamp || (b >= 0.f && b <= 1.f)) ? sc * db : 0.f;
+        }
+        float *const dst_img = LOSS ? la.v_out : out_img;
         if (vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H) {          // uniform over the CTA
             __syncthreads();                                                    // stage st is free: every warp left its loop
             float *s_out = reinterpret_cast<float *>(s_rec[st]);
@@ -228,11 +266,11 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
                 const float4 v = reinterpret_cast<const float4 *>(s_out)[tid];
                 const size_t off = ((size_t)(ty0 + row) * W + tx0) * 3 + 4 * q;
                 if (out_mc) multimem_st_v4(out_mc + off, v);
-                else *reinterpret_cast<float4 *>(out_img + off) = v;
+                else *reinterpret_cast<float4 *>(dst_img + off) = v;
             }
         } else if (inside) {
             if (out_mc) { multimem_st(out_mc + 3 * pix, r); multimem_st(out_mc + 3 * pix + 1, g); multimem_st(out_mc + 3 * pix + 2, b); }
-            else { out_img[3 * pix] = r; out_img[3 * pix + 1] = g; out_img[3 * pix + 2] = b; }
+            else { dst_img[3 * pix] = r; dst_img[3 * pix + 1] = g; dst_img[3 * pix + 2] = b; }
         }
         if (AUX && inside) {
             final_Ts[pix] = T_final;
@@ -240,6 +278,34 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
         }
         if (TMA) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes to the stage (s_out) before the next TMA into it
         __syncthreads();     // stage st, s_mask and s_list may be overwritten from here on
+    }
+    if (LOSS) {
+        __shared__ float s_red[RB / 32];
+        __shared__ bool s_last;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) sq_sum += __shfl_xor_sync(0xffffffffu, sq_sum, d);
+        if (lane == 0) s_red[warp] = sq_sum;
+        __syncthreads();
+        if (tid == 0) {
+            float t = 0.f;
+#pragma unroll
+            for (int w = 0; w < RB / 32; ++w) t += s_red[w];
+            la.partials[blockIdx.x] = t;
+            __threadfence();
+            s_last = atomicAdd(la.ticket, 1u) == gridDim.x - 1;
+        }
+        __syncthreads();
+        if (s_last && warp == 0) {                        // last CTA: fixed-order sum of the partials
+            __threadfence();
+            float t = 0.f;
+            for (int c = lane; c < (int)gridDim.x; c += 32) t += *reinterpret_cast<volatile float *>(la.partials + c);
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
+            if (lane == 0) {
+                *la.loss = t * la.inv_numel;
+                *la.ticket = 0;
+            }
+        }
     }
 }
 
@@ -272,7 +338,8 @@ struct GradOut {            // VEC12: g12 = (N,12) rows {v_xy.x, v_xy.y, v_conic
 template <bool TMA, bool VEC12>
 __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, const int *__restrict__ tile_bins,
                                                         const float4 *__restrict__ packed, GatherSrc src,
-                                                        const float *__restrict__ v_out, GradOut out) {
+                                                        const float *__restrict__ v_out, GradOut out,
+                                                        const float *__restrict__ v_scale = nullptr) {
     __shared__ __align__(128) float4 s_rec[RB * 3];
     __shared__ __align__(16) float s_v[3][GI2D_TILE_PIX];      // upstream gradient, one plane per channel
     __shared__ float s_part[9][2 * RB];                        // flushed partial sums, slot = thread + record
@@ -296,6 +363,10 @@ __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, co
         if (i < H && j < W) {
             const size_t pix = (size_t)i * W + j;
             vr = __ldg(v_out + 3 * pix); vg = __ldg(v_out + 3 * pix + 1); vb = __ldg(v_out + 3 * pix + 2);
+            if (v_scale) {                  // upstream gradient of a scalar loss whose d/d out_img is already in v_out
+                const float sc = __ldg(v_scale);
+                vr *= sc; vg *= sc; vb *= sc;
+            }
         }
         s_v[0][tid] = vr; s_v[1][tid] = vg; s_v[2][tid] = vb;
     }
@@ -570,6 +641,44 @@ int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *t
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     GradOut out{grads12, nullptr, nullptr, nullptr, nullptr};
     raster_bwd_kernel<true, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out, out);
+    return cuda_status();
+}
+
+// Loss epilogue: forward over the packed records that ends in the L2 loss the reference's training step
+// computes from the image (gaussianimage_cholesky.py:84-85 clamp + layout change, utils.py:20-25 F.mse_loss), and writes
+// d loss / d out_img into v_out for gi2d_raster_sum_bwd_packed_scaled.  The image itself is optional.
+int gi2d_raster_sum_fwd_packed_mse(int TX, int TY, int W, int H, int *tile_bins, const float *packed, const int *d_status,
+                                   const float *background, const float *gt, int gt_is_chw, int clamp01, float *v_out,
+                                   float *image, float *loss, void *ws, size_t ws_bytes, cudaStream_t stream) {
+    if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0 || !gt || !v_out || !loss || !ws) return GI2D_ERR_INVALID;
+    const int nt = TX * TY;
+    const int grid = fwd_grid(raster_fwd_kernel<true, false, true>, nt);
+    if (ws_bytes < sizeof(float) * (size_t)grid + 16) return GI2D_ERR_WORKSPACE;
+    LossArgs la{gt, gt_is_chw ? 1 : 0, clamp01 ? 1 : 0, 1.f / (3.f * (float)H * (float)W), v_out, image,
+                reinterpret_cast<float *>(reinterpret_cast<char *>(ws) + 16), reinterpret_cast<unsigned int *>(ws), loss};
+    GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
+    raster_fwd_kernel<true, false, true><<<grid, RB, 0, stream>>>(TX, W, H, 0, nt, tile_bins, reinterpret_cast<const float4 *>(packed), src,
+                                                                 d_status, background, nullptr, nullptr, nullptr, nullptr,
+                                                                 vec_ok(W, v_out), la);
+    return cuda_status();
+}
+
+// Workspace of gi2d_raster_sum_fwd_packed_mse: a ticket word (must be ZERO before the first call; the kernel leaves it
+// zero) and one partial sum per resident CTA.
+size_t gi2d_raster_mse_workspace_bytes(void) {
+    return 16 + sizeof(float) * (size_t)fwd_grid(raster_fwd_kernel<true, false, true>, 1 << 30);
+}
+
+// gi2d_raster_sum_bwd_packed with v_out multiplied by the device scalar *v_scale (the upstream gradient of the loss).
+int gi2d_raster_sum_bwd_packed_scaled(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
+                                      const float *v_out, const float *v_scale, float *grads12, cudaStream_t stream) {
+    if (N <= 0 || TX <= 0 || TY <= 0) return GI2D_ERR_INVALID;
+    if (reinterpret_cast<uintptr_t>(grads12) & 15) return GI2D_ERR_INVALID;
+    init_once();
+    cudaMemsetAsync(grads12, 0, sizeof(float) * 12 * (size_t)N, stream);
+    GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
+    GradOut out{grads12, nullptr, nullptr, nullptr, nullptr};
+    raster_bwd_kernel<true, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out, out, v_scale);
     return cuda_status();
 }
 

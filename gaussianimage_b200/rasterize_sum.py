@@ -201,7 +201,7 @@ _host_status = None
 
 class FusedResult:
     """Device tensors of one pass of the fused chain; gids_sorted / status are views made on demand."""
-    __slots__ = ("out_img", "final_Ts", "final_idx", "tile_bins", "packed", "_scratch", "_o_gids", "_o_status", "_cap")
+    __slots__ = ("out_img", "final_Ts", "final_idx", "tile_bins", "packed", "_scratch", "_o_gids", "_o_status", "_cap", "extra")
 
     @property
     def gids_sorted(self):
@@ -215,7 +215,8 @@ class FusedResult:
         return getattr(self, k)
 
 
-def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap, want_aux=False, host_slot=-1):
+def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap, want_aux=False, host_slot=-1,
+                raster=None):
     """One asynchronous pass of the fused chain (csrc/binning.cu gi2d_bin_fused + csrc/raster.cu packed forward) on the
     current stream with an intersection capacity `cap`.  Returns a FusedResult: out_img, final_Ts/final_idx (or None),
     tile_bins (T,2), packed (cap*12), gids_sorted (cap), status (2,) = [n, overflow].  host_slot >= 0 also publishes the
@@ -240,6 +241,10 @@ def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, 
                                        conics.data_ptr(), colors.data_ptr(), opacity.data_ptr(), cap, base, ws_bytes,
                                        base + o_gids, tile_bins.data_ptr(), packed.data_ptr(), base + o_status, host_ptr,
                                        stream), "bin_fused")
+    if raster is not None:                 # another consumer of the lists (loss.py: forward that ends in the loss)
+        r.out_img = r.final_Ts = r.final_idx = None
+        raster(r, base + o_status, stream)
+        return r
     r.out_img = out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
     r.final_Ts = final_Ts = torch.empty((H, W), dtype=torch.float32, device=dev) if want_aux else None
     r.final_idx = final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if want_aux else None
@@ -273,7 +278,7 @@ def set_memoise_binning(flag: bool):
     _geometry.clear()
 
 
-def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=False):
+def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=False, raster=None):
     """Rasterize the geometry of a previous fused_chain result with other conics / colours / opacities."""
     dev = xys.device
     L = lib()
@@ -287,6 +292,10 @@ def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=F
     base = src._scratch.data_ptr()
     check(L.gi2d_repack_records(cap, base + src._o_gids, base + src._o_status, xys.data_ptr(), conics.data_ptr(),
                                 colors.data_ptr(), opacity.data_ptr(), packed.data_ptr(), stream), "repack_records")
+    if raster is not None:
+        r.out_img = r.final_Ts = r.final_idx = None
+        raster(r, base + src._o_status, stream)
+        return r
     r.out_img = out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
     r.final_Ts = final_Ts = torch.empty((H, W), dtype=torch.float32, device=dev) if want_aux else None
     r.final_idx = final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if want_aux else None
@@ -296,7 +305,7 @@ def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=F
     return r
 
 
-def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background, want_aux):
+def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background, want_aux, raster=None):
     global _host_status, geometry_hits
     N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
     dev = xys.device
@@ -313,9 +322,11 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
         g = _geometry.get(gkey) if _memoise else None
         if g is not None and g.matches(xys, radii, nth, key):
             geometry_hits += 1
-            r = fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux)
+            r = fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux, raster)
             if g.n_isect is not None:
                 ctx.num_intersects = g.n_isect
+            if raster is not None:
+                return r
             ctx.save_for_backward(r.tile_bins, r.packed)
             return r.out_img, r.final_Ts
         while True:
@@ -323,7 +334,7 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
             if cap is None:
                 cap = _capacity[key] = max(4 * N, 1 << 14)
             slot = _host_status.acquire() if strict else -1
-            r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux, slot)
+            r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux, slot, raster)
             _last_status[dev.index] = (r._scratch, r._o_status, cap, key)
             n = None
             if not strict:
@@ -341,6 +352,8 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
             keep._scratch, keep._o_gids, keep._o_status, keep._cap, keep.tile_bins = r._scratch, r._o_gids, r._o_status, cap, r.tile_bins
             g.result, g.cap, g.n_isect = keep, cap, n
             _geometry[gkey] = g
+    if raster is not None:
+        return r
     ctx.save_for_backward(r.tile_bins, r.packed)
     return r.out_img, r.final_Ts
 

@@ -204,6 +204,21 @@ int gi2d_raster_sum_bwd(int N, int TX, int TY, int W, int H, const int *gids_sor
 int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
                                const float *v_out, float *grads12, cudaStream_t stream);
 
+/* ---- loss epilogue --------------------------------------------------------------------------------- */
+
+/* gi2d_raster_sum_fwd_packed that ends in the training loss the reference's callers compute next: image =
+ * clamp(out_img, 0, 1) in the target's layout (gaussianimage_cholesky.py:84-85), loss = F.mse_loss(image, gt)
+ * (utils.py:20-25).  gt: (3,H,W) planes when gt_is_chw else (H,W,3).  Writes *loss (deterministic), v_out (H,W,3) =
+ * d loss / d out_img (zero where the clamp is active), and optionally the clamped image (H,W,3; NULL to skip).
+ * ws: gi2d_raster_mse_workspace_bytes() bytes whose first word is ZERO before the first call (the kernel resets it). */
+size_t gi2d_raster_mse_workspace_bytes(void);
+int gi2d_raster_sum_fwd_packed_mse(int TX, int TY, int W, int H, int *tile_bins, const float *packed, const int *d_status,
+                                   const float *background, const float *gt, int gt_is_chw, int clamp01, float *v_out,
+                                   float *image, float *loss, void *ws, size_t ws_bytes, cudaStream_t stream);
+/* gi2d_raster_sum_bwd_packed with v_out multiplied by the DEVICE scalar *v_scale (the upstream gradient of the loss). */
+int gi2d_raster_sum_bwd_packed_scaled(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
+                                      const float *v_out, const float *v_scale, float *grads12, cudaStream_t stream);
+
 /* ---- optimizer step -------------------------------------------------------------------------- */
 
 /* The Adan update of optimizer.py:232-279 (`_single_tensor_adan`; optimizer.py:296-362 is the same arithmetic as ~25
