@@ -5,7 +5,7 @@
 // neither vendors nor pins) and calls adan_multi_tensor / adan_single_tensor.
 //
 // HBM-bound elementwise work: 6 arrays read, 5 (6 when the gradient is clipped) written, 44 B per element; float4
-// accesses, a block owns 4096 consecutive elements of one tensor, the (tensor, chunk) of a block comes from a table
+// accesses, a block owns 1024 consecutive elements of one tensor, the (tensor, chunk) of a block comes from a table
 // passed by value.  Two ways to supply the scalars:
 //   host   the ten floats the reference passes (bias corrections computed by the host in double, optimizer.py:169-171);
 //   device hyper-parameters and the step counter live in device memory, bias corrections are computed in double on
@@ -20,7 +20,7 @@ namespace gi2d {
 
 constexpr int ADAN_MAX_TENSORS = 16;
 constexpr int ADAN_THREADS = 256;
-constexpr int ADAN_CHUNK = ADAN_THREADS * 16;     // elements per block
+constexpr int ADAN_CHUNK = ADAN_THREADS * 4;      // elements per block: one float4 per thread and array (C2: 547 blocks)
 
 struct AdanTable {
     float *p[ADAN_MAX_TENSORS], *g[ADAN_MAX_TENSORS], *m[ADAN_MAX_TENSORS], *v[ADAN_MAX_TENSORS], *d[ADAN_MAX_TENSORS],

@@ -99,7 +99,7 @@ def main():
     chol = torch.nn.Parameter(d.cholesky.clone())
     cols = torch.nn.Parameter(d.colors.clone())
     G.set_sync_free(True)
-    for capt, key in ((False, "foreach"), (True, "fused")):
+    for capt, key in ((False, "foreach"), (True, "fused"), (True, "fused_and_loss_epilogue")):
         ps = [torch.nn.Parameter(x.detach().clone()) for x in (means, chol, cols)]
         o = Adan(ps, lr=0.018, capturable=True) if capt else None
         st = [[torch.zeros_like(p) for p in ps] for _ in range(4)]
@@ -108,8 +108,11 @@ def main():
             for p in ps:
                 p.grad = None
             xys, depths, radii, conics, nth = G.project_gaussians_2d(torch.tanh(ps[0]), ps[1], s.H, s.W, s.tile_bounds)
-            out = G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, ps[2], d.opacity, s.H, s.W)
-            loss = torch.nn.functional.mse_loss(out, d.gt)
+            if key == "fused_and_loss_epilogue":
+                loss = G.rasterize_gaussians_sum_mse(xys, depths, radii, conics, nth, ps[2], d.opacity, s.H, s.W, d.gt, clamp=False)
+            else:
+                out = G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, ps[2], d.opacity, s.H, s.W)
+                loss = torch.nn.functional.mse_loss(out, d.gt)
             loss.backward()
             if capt:
                 o.step()

@@ -20,23 +20,35 @@ traffic = {}
 print("| kernel | " + " | ".join(k for _, k in KEYS) + " | top stalls (pc samples) |")
 print("|---|" + "---|" * (len(KEYS) + 1))
 for rep in sys.argv[1:]:
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    raw = Path(rep).read_text() if rep.endswith(".csv") else \
+        subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     if len(rows) < 3:
         continue
     hdr, units = rows[0], rows[1]
     idx = {h: i for i, h in enumerate(hdr)}
-    r = rows[-1]                       # last captured launch (steady state)
-    name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "")
-    cells = []
-    for key, _ in KEYS:
-        cells.append(f"{r[idx[key]]} {units[idx[key]]}".strip() if key in idx else "-")
-    stalls = sorted(((float(r[i]), h.replace("smsp__pcsamp_warps_issue_stalled_", "")) for h, i in idx.items()
-                     if h.startswith("smsp__pcsamp_warps_issue_stalled_") and not h.endswith("_not_issued") and r[i]), reverse=True)[:4]
-    print(f"| `{name}` | " + " | ".join(cells) + " | " + ", ".join(f"{n} {int(v)}" for v, n in stalls) + " |")
-    def b(key):
-        return float(r[idx[key]]) * UNIT.get(units[idx[key]], 1.0)
-    short = next((k for k in ("raster_bwd", "raster_fwd", "scan_kernel", "onesweep", "project_fwd", "project_bwd") if k in name), name)
-    traffic[short] = {"dram_bytes": b("dram__bytes_read.sum") + b("dram__bytes_write.sum"), "us": float(r[idx["gpu__time_duration.sum"]]),
-                      "report": Path(rep).name}
+    seen = {}
+    for r in rows[2:]:                 # one line per distinct kernel of the report; the last launch of each wins
+        if len(r) == len(hdr) and "at::" not in r[idx["Kernel Name"]]:      # the path's kernels, not torch's
+            seen[r[idx["Kernel Name"]] + "|" + r[idx["Grid Size"]]] = r
+    if not seen:
+        seen = {"last": rows[-1]}
+    for r in seen.values():
+        name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "")
+        cells = []
+        for key, _ in KEYS:
+            cells.append(f"{r[idx[key]]} {units[idx[key]]}".strip() if key in idx else "-")
+        stalls = sorted(((float(r[i]), h.replace("smsp__pcsamp_warps_issue_stalled_", "")) for h, i in idx.items()
+                         if h.startswith("smsp__pcsamp_warps_issue_stalled_") and not h.endswith("_not_issued") and r[i]), reverse=True)[:4]
+        print(f"| `{name}` grid {r[idx['Grid Size']]} | " + " | ".join(cells) + " | " + ", ".join(f"{n} {int(v)}" for v, n in stalls) + " |")
+
+        def b(key):
+            return float(r[idx[key]]) * UNIT.get(units[idx[key]], 1.0)
+        short = next((k for k in ("raster_bwd", "raster_fwd", "bin_small", "scan_kernel", "onesweep", "decode_project", "project_fwd",
+                                  "project_bwd", "tile_sort_pack", "tile_count_scatter", "tile_scan", "repack", "adan") if k in name), name)
+        if short == "raster_fwd" and "true, false, true" in r[idx["Kernel Name"]].replace("1, 0, 1", "true, false, true"):
+            short = "raster_fwd_loss"
+        traffic[short + ("@c5" if Path(rep).stem.endswith("c5") else "")] = {
+            "dram_bytes": b("dram__bytes_read.sum") + b("dram__bytes_write.sum"), "us": float(r[idx["gpu__time_duration.sum"]]),
+            "report": Path(rep).name}
 Path("profiles/ncu_traffic.json").write_text(json.dumps(traffic, indent=1) + "\n")
