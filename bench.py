@@ -583,7 +583,7 @@ def run_decode8k(args, rank, world, dev):
     scale, beta = torch.tensor([1.0 / 63] * 3), torch.zeros(3)
     chol_q = torch.round((sc.cholesky - torch.tensor([0.5, 0.0, 0.5]) - beta) / scale).clamp(0, 63).to(torch.uint8)
     cb = torch.rand(2, 8, 3, generator=g) * 0.5
-    idx = torch.randint(0, 8, (N, 2), generator=g)
+    idx = torch.randint(0, 8, (N, 2), generator=g).to(torch.int32)       # decompress() hands the indices over as .int() (gaussianimage_cholesky.py:211)
     host = [t.contiguous().pin_memory() for t in (xyz_h, chol_q, idx)]
     d_in = [t.to(dev) for t in host]
     scale, beta, cb = scale.to(dev), beta.to(dev), cb.to(dev)
@@ -609,9 +609,10 @@ def run_decode8k(args, rank, world, dev):
         colors = cb[0][d_in[2][:, 0]] + cb[1][d_in[2][:, 1]]                  # quantize.py:146-150 (residual VQ lookup)
         return (renderer or R).render(means, chol, colors, opacity)
 
-    def decode(renderer=None):
+    def decode(renderer=None, bufs=None):
         # the same, with the de-quantisation prologue fused into the projection kernel (gaussianimage_b200/decode.py)
-        return (renderer or R).render_compressed(d_in[0], d_in[1], scale, beta, bound, d_in[2], cb, opacity)
+        b = bufs or d_in
+        return (renderer or R).render_compressed(b[0], b[1], scale, beta, bound, b[2], cb, opacity)
 
     def barrier():
         torch.cuda.synchronize()
@@ -646,22 +647,41 @@ def run_decode8k(args, rank, world, dev):
             barrier()
             dist.all_reduce(t2, op=dist.ReduceOp.MAX)
             nccl_ms = t2.item() / K
-        # e2e: compressed parameters from pinned host memory every frame, a scalar checksum of the frame back
+        # e2e: compressed parameters from pinned host memory every frame, a scalar checksum of the frame back.  Two frames
+        # in flight: the H2D copy of frame i+1 runs on a copy stream into the other input set while frame i decodes, and the
+        # host reads frame i's checksum while frame i+1 is in flight.
         cur = torch.cuda.current_stream()
-        res = torch.empty(1, dtype=torch.float32).pin_memory()
+        copy_stream = torch.cuda.Stream()
+        sets = [d_in, [t.clone() for t in d_in]]
+        res = [torch.empty(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+        ev_copy = [torch.cuda.Event() for _ in range(2)]
+        ev_done = [torch.cuda.Event() for _ in range(2)]
 
-        def e2e_step():
-            for dst, src in zip(d_in, host):
-                dst.copy_(src, non_blocking=True)
-            frame = decode()
-            res.copy_(frame[::16, ::16].mean().view(1), non_blocking=True)
-            cur.synchronize()
-        for _ in range(3):
-            e2e_step()
+        def enqueue(i):
+            k = i & 1
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(ev_done[k])            # frame i-2 no longer reads this input set
+                for dst, src in zip(sets[k], host):
+                    dst.copy_(src, non_blocking=True)
+                ev_copy[k].record(copy_stream)
+            cur.wait_event(ev_copy[k])
+            frame = decode(None, sets[k])
+            res[k].copy_(frame[::16, ::16].mean().view(1), non_blocking=True)
+            ev_done[k].record(cur)
+
+        def e2e_run(n):
+            for i in range(n):
+                enqueue(i)
+                if i:
+                    ev_done[(i - 1) & 1].synchronize()          # host consumes frame i-1 while frame i is in flight
+                    float(res[(i - 1) & 1][0])
+            ev_done[(n - 1) & 1].synchronize()
+        for e in ev_done:
+            e.record(cur)
+        e2e_run(4)
         barrier()
         t0 = time.perf_counter()
-        for _ in range(K):
-            e2e_step()
+        e2e_run(K)
         torch.cuda.synchronize()
         e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
@@ -686,7 +706,7 @@ def run_decode8k(args, rank, world, dev):
                    "peaks": peaks_src},
         "clocks": clk.summary(),
         "e2e": {"value": K / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in host),
-                "d2h_bytes_per_step": 4, "mode": "compressed parameters H2D from pinned memory per frame; frame checksum D2H"},
+                "d2h_bytes_per_step": 4, "mode": "compressed parameters (fp16 positions, uint8 Cholesky codes, int32 codebook indices) H2D from pinned memory every frame on a copy stream, double-buffered; frame checksum D2H and host read every frame; two frames in flight"},
         "gpu_launches": (2 + _gi2d_lib().gi2d_bin_fused_kernel_count(N, (W + 15) // 16, (H + 15) // 16)) * K,   # decode+project, binning chain, rasterizer
         "roofline": {"bound": "hbm", "achieved": (frame_bytes / world * (2 if world > 1 else 1)) / 1e9 / (total_ms / K / 1e3),
                      "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": None,

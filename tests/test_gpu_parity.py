@@ -606,3 +606,36 @@ def test_model_forward_under_graph_capture_reuses_the_binning():
     # eager calls after the capture must not touch the captured entry
     _, e_out, _, _ = _model_forward(d, s, colors, opac)
     assert torch.equal(e_out, w_out)
+
+
+# ------------------------------------------------------------------------------- randomised sweep
+@pytest.mark.parametrize("case", range(12))
+def test_random_shapes_lists_bins_image_and_gradients(case):
+    """Seeded random image sizes (mostly not multiples of 16), Gaussian counts and densities: tile lists and bin edges
+    bit-exact against the oracle, image and fit-step gradients within the north_star tolerances."""
+    rng = np.random.default_rng(1000 + case)
+    H, W = int(rng.integers(17, 260)), int(rng.integers(17, 330))
+    N = int(rng.choice([1, 2, 31, 33, 255, 257, 1000, 2500, 4097]))
+    dense = float(rng.choice([0.0, 0.0, 0.3, 0.6]))
+    s = make_scene(H, W, N, seed=int(rng.integers(1, 10_000)), dense=dense)
+    _, st = oracle_chain(s)
+    f = _fused_internals(s.to(DEV), s)
+    T = s.tile_bounds[0] * s.tile_bounds[1]
+    assert f["n"] == st["n"]
+    assert np.array_equal(_np(f["gids_sorted"]), st["gaussian_ids_sorted"])
+    if st["n"] > 0:
+        bins = _np(f["tile_bins"]).copy()
+        bins[bins[:, 0] >= bins[:, 1]] = 0                       # empty tiles: (0, 0) in the reference
+        assert np.array_equal(bins, st["tile_bins"][:T])
+        want, _, w_fidx, amb = O.rasterize_sum_forward(s.H, s.W, st["gaussian_ids_sorted"], st["tile_bins"], st["xys"], st["conics"],
+                                                     _np(s.colors), _np(s.opacity), want_ambig=True)
+        amb = amb.astype(bool)
+        assert_image_close(_np(f["out"]), want, f"image {H}x{W} N={N} dense={dense}", exclude=amb)
+        assert np.array_equal(_np(f["fidx"])[~amb], w_fidx[~amb])
+    out, loss, g_mean, g_L, _, g_col, g_op = _fit_step_gpu(s.to(DEV), s)
+    w_loss, w = O.fit_step_cholesky(_np(s.means2d), _np(s.cholesky), _np(s.colors), _np(s.opacity), _np(s.gt), s.H, s.W)
+    assert abs(loss.item() - w_loss) <= 1e-5 * abs(w_loss)
+    assert_grad_close(_np(g_mean), w["v_means2d"], "d loss / d means2d")
+    assert_grad_close(_np(g_L), w["v_L"], "d loss / d L_elements")
+    assert_grad_close(_np(g_col), w["v_colors"], "d loss / d colors")
+    assert_grad_close(_np(g_op), w["v_opacity"], "d loss / d opacity")
