@@ -130,10 +130,11 @@ def run_reference(args):
     """--impl reference: the CPU restatement of the reference path on the box's host cores (rank 0 only)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    from gaussianimage_b200.synth import make_scene
+    cores = os.cpu_count()
+    os.environ["OMP_NUM_THREADS"] = str(cores)            # torchrun sets it to 1 per rank; this arm runs alone on rank 0 and
+    from gaussianimage_b200.synth import make_scene      # may use every host thread (set before the OpenMP runtime starts)
     name, H, W, N, param = workload_config(args)
     scene = make_scene(H, W, N, seed=1)
-    cores = os.cpu_count()
     per_step = []
     fn = cpu_step_fn(scene, param, "fit" if args.workload == "fit" else "render")
     for _ in range(max(1, min(args.warmup, 3))):
