@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
     __shared__ int2 s_range[NSTAGE];
     __shared__ uint8_t s_mask[RB];
     __shared__ uint8_t s_list[RB / 32][RB];
+    __shared__ __align__(16) float s_out[GI2D_TILE_PIX * 3];          // output tile staging (its own buffer: no stage is aliased)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int stride = gridDim.x;
@@ -145,6 +146,9 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
             tma_load_1d(s_rec[st], packed + 3 * (size_t)rg.x, (uint32_t)c * 48u, &s_bar[st]);
         }
     };
+    // Barriers per tile: ONE after the culling masks and ONE after the output tile is staged.  The second one also says
+    // "every warp has left the evaluation loop", i.e. the tile's record stage is free: thread 0 re-arms it right there
+    // with the copy for the tile after next, so a copy always has a whole tile of evaluation to land.
     int2 r_next = make_int2(0, 0);
     if (TMA) {
         if (tid == 0) {
@@ -152,23 +156,20 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
             mbar_init(&s_bar[NSTAGE - 1], 1);
             fence_mbar_init();
             issue(0, fetch_range(k));
-            if (k + stride < n_tiles) r_next = fetch_range(k + stride);
+            if (k + stride < n_tiles) issue(NSTAGE - 1, fetch_range(k + stride));
+            if (k + 2 * stride < n_tiles) r_next = fetch_range(k + 2 * stride);
         }
+        __syncthreads();                                  // barrier initialisation and s_range[] visible
     }
     uint32_t phase_bits = 0;                              // bit st = parity of the next completion of s_bar[st]
     float sq_sum = 0.f;                                   // LOSS: this thread's share of the squared error
 
     for (int it = 0; k < n_tiles; k += stride, ++it) {
         const int st = TMA ? (it & 1) : 0;
-        if (TMA) {
-            if (tid == 0 && k + stride < n_tiles) {       // stage st^1 was released by the barrier that ended iteration it-1
-                issue(st ^ 1, r_next);
-                if (k + 2 * stride < n_tiles) r_next = fetch_range(k + 2 * stride);
-            }
-        } else if (tid == 0) {
-            s_range[0] = bins2[tile_begin + k];
+        if (!TMA) {
+            if (tid == 0) s_range[0] = bins2[tile_begin + k];
+            __syncthreads();
         }
-        __syncthreads();                                  // s_range[st] (and the barrier initialisation) visible
         const int tile = tile_begin + k;
         const int ty = tile / TX, tx = tile - ty * TX;
         const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
@@ -200,7 +201,9 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
                 }
                 s_mask[tid] = (uint8_t)m;
             }
-            __syncthreads();
+        }
+        __syncthreads();             // masks visible; also: the previous tile's readers of s_out are done (empty tiles included)
+        if (cnt > 0) {
             // per-warp compaction of the record indices whose extent touches this warp's pixel block
             int nlist = 0;
             for (int c = 0; c < cnt; c += 32) {
@@ -255,12 +258,17 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
             b = (!la.clamp || (b >= 0.f && b <= 1.f)) ? sc * db : 0.f;
         }
         float *const dst_img = LOSS ? la.v_out : out_img;
-        if (vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H) {          // uniform over the CTA
-            __syncthreads();                                                    // stage st is free: every warp left its loop
-            float *s_out = reinterpret_cast<float *>(s_rec[st]);
+        const bool vec_tile = vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H;     // uniform over the CTA
+        if (vec_tile) {
             const int lp = (by * 4 + (lane >> 3)) * GI2D_TILE + bx * 8 + (lane & 7);
             s_out[3 * lp] = r; s_out[3 * lp + 1] = g; s_out[3 * lp + 2] = b;
-            __syncthreads();
+        }
+        __syncthreads();             // output tile staged; every warp has left its loop: stage st, s_mask, s_list are free
+        if (TMA && tid == 0 && k + 2 * stride < n_tiles) {
+            issue(st, r_next);                                                  // tile after next, into the stage just left
+            if (k + 3 * stride < n_tiles) r_next = fetch_range(k + 3 * stride);
+        }
+        if (vec_tile) {
             if (tid < 192) {
                 const int row = tid / 12, q = tid - row * 12;
                 const float4 v = reinterpret_cast<const float4 *>(s_out)[tid];
@@ -276,8 +284,6 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
             final_Ts[pix] = T_final;
             final_idx[pix] = cur;
         }
-        if (TMA) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic writes to the stage (s_out) before the next TMA into it
-        __syncthreads();     // stage st, s_mask and s_list may be overwritten from here on
     }
     if (LOSS) {
         __shared__ float s_red[RB / 32];
