@@ -430,7 +430,8 @@ __global__ void __launch_bounds__(SB) onesweep_kernel(const uint32_t *__restrict
                 const float o = __ldg(ps.opac + g);
                 __stcs(ps.packed + 3 * (size_t)pos + 0, make_float4(x, y, o, cx));
                 __stcs(ps.packed + 3 * (size_t)pos + 1, make_float4(cy, cz, r, gg));
-                __stcs(ps.packed + 3 * (size_t)pos + 2, make_float4(b, __int_as_float(v), 0.f, 0.f));
+                const float2 e = record_extent(cx, cy, cz, o);
+                __stcs(ps.packed + 3 * (size_t)pos + 2, make_float4(b, __int_as_float(v), e.x, e.y));
             }
         }
     }
@@ -662,6 +663,7 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
     if (a.dbg & 32) return;
     // ---- phase 4: scatter gid + packed record to the final slot
     const int grp = warp >> 3;
+    const float2 rext = record_extent(rcx, rcy, rcz, ro);      // once per Gaussian; every intersection's record carries it
     warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int gid, int owner, bool active) {
         const unsigned peers = __match_any_sync(0xffffffffu, active ? tile : -1 - lane);
         int pos = 0;
@@ -675,11 +677,12 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
         const float x = __shfl_sync(0xffffffffu, rx, owner), y = __shfl_sync(0xffffffffu, ry, owner), o = __shfl_sync(0xffffffffu, ro, owner);
         const float cx = __shfl_sync(0xffffffffu, rcx, owner), cy = __shfl_sync(0xffffffffu, rcy, owner), cz = __shfl_sync(0xffffffffu, rcz, owner);
         const float r = __shfl_sync(0xffffffffu, rr, owner), gg = __shfl_sync(0xffffffffu, rg, owner), bl = __shfl_sync(0xffffffffu, rb, owner);
+        const float ex = __shfl_sync(0xffffffffu, rext.x, owner), ey = __shfl_sync(0xffffffffu, rext.y, owner);
         if (active && pos < a.capacity) {
             a.gids_sorted[pos] = gid;
             __stcs(a.packed + 3 * (size_t)pos + 0, make_float4(x, y, o, cx));
             __stcs(a.packed + 3 * (size_t)pos + 1, make_float4(cy, cz, r, gg));
-            __stcs(a.packed + 3 * (size_t)pos + 2, make_float4(bl, __int_as_float(gid), 0.f, 0.f));
+            __stcs(a.packed + 3 * (size_t)pos + 2, make_float4(bl, __int_as_float(gid), ex, ey));
         }
     });
 }
@@ -883,7 +886,8 @@ __global__ void __launch_bounds__(256) tile_count_scatter_kernel(ScatterArgs a) 
         const float o = __ldg(a.opac + q);
         a.rows[3 * q + 0] = make_float4(x, y, o, cx);
         a.rows[3 * q + 1] = make_float4(cy, cz, r, gg);
-        a.rows[3 * q + 2] = make_float4(b, __int_as_float(i), 0.f, 0.f);
+        const float2 e = record_extent(cx, cy, cz, o);
+        a.rows[3 * q + 2] = make_float4(b, __int_as_float(i), e.x, e.y);
     }
     warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int gid, int, bool active) {
         if (!active) return;
@@ -1014,7 +1018,8 @@ __global__ void __launch_bounds__(256) repack_kernel(int capacity, const int *__
         const float o = __ldg(opac + g);
         __stcs(packed + 3 * (size_t)i + 0, make_float4(x, y, o, cx));
         __stcs(packed + 3 * (size_t)i + 1, make_float4(cy, cz, r, gg));
-        __stcs(packed + 3 * (size_t)i + 2, make_float4(b, __int_as_float(v), 0.f, 0.f));
+        const float2 e = record_extent(cx, cy, cz, o);
+        __stcs(packed + 3 * (size_t)i + 2, make_float4(b, __int_as_float(v), e.x, e.y));
     }
 }
 

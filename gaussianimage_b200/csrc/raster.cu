@@ -53,7 +53,8 @@ __device__ __forceinline__ void stage_records(float4 *s_rec, uint64_t *bar, cons
             const float o = __ldg(src.opac + g);
             s_rec[3 * tid + 0] = make_float4(x, y, o, cx);
             s_rec[3 * tid + 1] = make_float4(cy, cz, r, gg);
-            s_rec[3 * tid + 2] = make_float4(b, __int_as_float(g), 0.f, 0.f);
+            const float2 e = record_extent(cx, cy, cz, o);
+            s_rec[3 * tid + 2] = make_float4(b, __int_as_float(g), e.x, e.y);
         }
         __syncthreads();
     }
@@ -61,11 +62,10 @@ __device__ __forceinline__ void stage_records(float4 *s_rec, uint64_t *bar, cons
 
 // Local (tile-relative, inclusive) pixel rectangle in which the record can pass the alpha test.
 // Returns false for "never visible in this tile".
-__device__ __forceinline__ bool record_rect(const float4 &A, const float4 &B, int tx0, int ty0, int &lx0, int &lx1, int &ly0,
+__device__ __forceinline__ bool record_rect(const float4 &A, const float4 &C, int tx0, int ty0, int &lx0, int &lx1, int &ly0,
                                             int &ly1) {
-    float ex, ey;
+    const float ex = C.z, ey = C.w;                       // carried in the record (record_extent): +inf = whole tile
     lx0 = 0; lx1 = GI2D_TILE - 1; ly0 = 0; ly1 = GI2D_TILE - 1;
-    if (!visible_extent(A.w, B.x, B.y, A.z, ex, ey)) return true;       // no bound: whole tile
     if (ex < 0.f) return false;
     // pixel centres sit at integer coordinates (px = (float)j, forward.cu:537-538)
     const float fx0 = ceilf(A.x - ex) - (float)tx0, fx1 = floorf(A.x + ex) - (float)tx0;
@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
             if (tid < cnt) {
                 int lx0, lx1, ly0, ly1;
                 uint32_t m = 0;
-                if (record_rect(rec[3 * tid], rec[3 * tid + 1], tx0, ty0, lx0, lx1, ly0, ly1)) {
+                if (record_rect(rec[3 * tid], rec[3 * tid + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
                     const uint32_t colm = (lx0 <= 7 ? 1u : 0u) | (lx1 >= 8 ? 2u : 0u);      // which 8-wide halves
 #pragma unroll
                     for (int q = 0; q < 4; ++q)
@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, co
     {
         int lx0 = 0, lx1 = 0, ly0 = 0, ly1 = 0;
         uint32_t rect = 0;
-        if (tid < cnt && record_rect(s_rec[3 * tid], s_rec[3 * tid + 1], tx0, ty0, lx0, lx1, ly0, ly1)) {
+        if (tid < cnt && record_rect(s_rec[3 * tid], s_rec[3 * tid + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
             const int g0 = lx0 >> 2, segs = (lx1 >> 2) - g0 + 1, rows = ly1 - ly0 + 1;
             units = rows * segs;
             rect = (uint32_t)lx0 | ((uint32_t)lx1 << 4) | ((uint32_t)ly0 << 8) | ((uint32_t)g0 << 12) | ((uint32_t)segs << 14) |

@@ -125,7 +125,9 @@ int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *ti
  *   gids_sorted (capacity) int32,
  *   tile_bins (TX*TY,2) int32: [lo,hi) per tile; empty tiles hold (INT_MAX, 0) until gi2d_raster_sum_fwd_packed
  *     rewrites them to the reference's (0, 0) -- consumers must treat lo >= hi as empty,
- *   packed (capacity*12 floats): per sorted intersection {x,y,opacity,conic.x | conic.y,conic.z,r,g | b,gid,0,0}
+ *   packed (capacity*12 floats): per sorted intersection {x,y,opacity,conic.x | conic.y,conic.z,r,g | b,gid,ex,ey}
+ *     (ex, ey: half-extents in pixels of the region where the alpha test can pass -- +inf = unbounded, -1 = never; the
+ *     rasterizers cull with them)
  *   status_out (2) int32: [0] = n_isect, [1] = 1 if n_isect > capacity (outputs truncated; retry with more).
  * Requires all depths == 0 (true for both 2D projections). n_isect < 2^30. */
 size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity);
