@@ -164,14 +164,16 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
     uint32_t phase_bits = 0;                              // bit st = parity of the next completion of s_bar[st]
     float sq_sum = 0.f;                                   // LOSS: this thread's share of the squared error
 
-    for (int it = 0; k < n_tiles; k += stride, ++it) {
+    // tile coordinates advance by (stride / TX, stride % TX) per iteration: no division inside the loop
+    const int step_y = stride / TX, step_x = stride - step_y * TX;
+    int ty = (tile_begin + k) / TX, tx = (tile_begin + k) - ty * TX;
+    for (int it = 0; k < n_tiles; k += stride, ++it, tx += step_x, ty += step_y) {
         const int st = TMA ? (it & 1) : 0;
         if (!TMA) {
             if (tid == 0) s_range[0] = bins2[tile_begin + k];
             __syncthreads();
         }
-        const int tile = tile_begin + k;
-        const int ty = tile / TX, tx = tile - ty * TX;
+        if (tx >= TX) { tx -= TX; ++ty; }
         const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
         const int j = tx0 + bx * 8 + (lane & 7), i = ty0 + by * 4 + (lane >> 3);
         const bool inside = i < H && j < W;
