@@ -487,7 +487,30 @@ struct SmallArgs {
     int *status_out;
     volatile int *status_host;
     int dbg;                  // experiments: stop after phase 1 / 2 / 3 (bits 8 / 16 / 32)
+    unsigned int *bar;        // {arrival count, generation}: library-owned, zero once, left zero-count by every barrier; null = cg grid.sync
 };
+
+// Grid-wide barrier of a co-resident (cooperatively launched) grid on two words of ordinary device memory: sense reversal,
+// the last block to arrive resets the count and advances the generation.  Self-cleaning, so the words are zeroed once per
+// (device, stream) and never again -- no memset node in front of the kernel.
+__device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int nb) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int g, old, v;
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(bar + 1) : "memory");   // cannot advance before this block arrives
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(bar) : "memory");
+        if (old == nb - 1) {
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(bar), "r"(0u) : "memory");
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar + 1) : "memory");
+        } else {
+            do {
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar + 1) : "memory");
+            } while (v == g);
+            asm volatile("fence.acq_rel.gpu;" ::: "memory");
+        }
+    }
+    __syncthreads();
+}
 
 // Calls f(tile, gid_or_0, owner_lane, active) for every (Gaussian, tile) pair of the warp, 32 pairs per round, in
 // emission order.  All 32 lanes call f in every round (f may use warp-wide primitives).
@@ -585,7 +608,7 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
     // grid-wide barrier (cooperative launch: all blocks are co-resident, the barrier state belongs to the driver, so
     // this path needs no zero-initialised memory at all)
     __threadfence();
-    cooperative_groups::this_grid().sync();
+    if (a.bar) grid_barrier(a.bar, gridDim.x); else cooperative_groups::this_grid().sync();
     // ---- phase 3a: exclusive scan over the BLOCKS of every tile column, in place, one warp per 4 tile columns (work
     // shared by all warps of the grid; O(blocks x tiles) traffic in total instead of every block reading the matrix)
     {
@@ -622,7 +645,7 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
         }
     }
     __threadfence();
-    cooperative_groups::this_grid().sync();
+    if (a.bar) grid_barrier(a.bar, gridDim.x); else cooperative_groups::this_grid().sync();
     if (a.dbg & 64) return;
     // ---- phase 3b: first slot of every tile = exclusive scan of the totals in tile order + the preceding blocks
     constexpr int PER = TP / NT;                               // consecutive tiles per thread
@@ -1129,6 +1152,31 @@ int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *ti
 
 // Number of kernels gi2d_bin_fused launches for this shape on the current device (1 = the one-kernel path; otherwise the
 // scan kernel + one onesweep pass per 8 tile-id bits); the zero-fill of the chain's control block is a memset, not a kernel.
+// Barrier words of the one-kernel path: a pool of 64 pairs per device, allocated and zeroed at the first call outside a
+// stream capture; a stream always maps to the same pair (work on one stream is serial, so a pair is not shared by two
+// grids unless two streams collide in the pool AND run this kernel at the same moment -- it occupies nearly every SM).
+// GI2D_OWN_BARRIER=0, or a first call inside a capture, falls back to cooperative-groups' grid.sync().
+static unsigned int *small_barrier(cudaStream_t stream) {
+    static const int own = env_int("GI2D_OWN_BARRIER", 1);
+    if (!own) return nullptr;
+    static unsigned int *pool[16] = {nullptr};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 16) return nullptr;
+    if (!pool[dev]) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        unsigned int *p = nullptr;
+        if (cudaMalloc(&p, 64 * 256) != cudaSuccess || cudaMemset(p, 0, 64 * 256) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        pool[dev] = p;
+    }
+    const uintptr_t h = reinterpret_cast<uintptr_t>(stream);
+    return pool[dev] + 64 * ((h >> 4 ^ h >> 12 ^ h >> 20) & 63);      // 256-byte slots
+}
+
 // GI2D_SCATTER_BIN: 0 = never, 1 (default) = images of more than 4096 tiles, 2 = whenever the one-kernel path does not apply
 static bool use_scatter(int T) {
     static const int mode = env_int("GI2D_SCATTER_BIN", 1);
@@ -1179,7 +1227,8 @@ int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, 
         if (sp.fn) {
             SmallArgs a{N, TX, TY, T, capacity, xys, radii, num_tiles_hit, conics, colors, opacities,
                         reinterpret_cast<uint32_t *>(base + L.mat), reinterpret_cast<uint32_t *>(base + L.mat) + (size_t)((N + 255) / 256) * sp.tp,
-                        ctl, gids_sorted, tile_bins, reinterpret_cast<float4 *>(packed), status_out, status_host, dbg};
+                        ctl, gids_sorted, tile_bins, reinterpret_cast<float4 *>(packed), status_out, status_host, dbg,
+                        small_barrier(stream)};
             void *args[] = {&a};
             const cudaError_t e = cudaLaunchCooperativeKernel(sp.fn, dim3((N + sp.nt - 1) / sp.nt), dim3(sp.nt), args, sp.smem, stream);
             return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
