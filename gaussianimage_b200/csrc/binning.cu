@@ -609,39 +609,36 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
     // this path needs no zero-initialised memory at all)
     __threadfence();
     if (a.bar) grid_barrier(a.bar, gridDim.x); else cooperative_groups::this_grid().sync();
-    // ---- phase 3a: exclusive scan over the BLOCKS of every tile column, in place, one warp per 4 tile columns (work
-    // shared by all warps of the grid; O(blocks x tiles) traffic in total instead of every block reading the matrix)
+    // ---- phase 3a: exclusive scan over the BLOCKS of every tile column, in place.  ONE column per warp, columns dealt
+    // round-robin over the blocks first (every SM takes part; with 4 columns per warp only the first quarter of the grid
+    // worked while the rest waited at the barrier below): up to 160 rows are in flight per pass, 5 per lane.
     {
-        const int gwarp = b * SMALL_WARPS + warp, nwarps = nb * SMALL_WARPS;
-        for (int item = gwarp; item < TP / 4; item += nwarps) {
-            uint4 *col = reinterpret_cast<uint4 *>(a.mat) + item;
-            uint4 carry = make_uint4(0, 0, 0, 0);
-            for (int r0 = 0; r0 < nb; r0 += 128) {             // 4 row batches in flight
-                uint4 v[4];
+        const int gwarp = warp * nb + b, nwarps = nb * SMALL_WARPS;
+        for (int item = gwarp; item < TP; item += nwarps) {
+            uint32_t *col = a.mat + item;
+            uint32_t carry = 0;
+            for (int r0 = 0; r0 < nb; r0 += 160) {
+                uint32_t v[5];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < 5; ++u) {
                     const int r = r0 + 32 * u + lane;
-                    v[u] = r < nb ? __ldcg(col + (size_t)r * (TP / 4)) : make_uint4(0, 0, 0, 0);
+                    v[u] = r < nb ? __ldcg(col + (size_t)r * TP) : 0u;
                 }
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < 5; ++u) {
                     if (r0 + 32 * u >= nb) break;
                     const int r = r0 + 32 * u + lane;
-                    uint4 in = v[u];
+                    uint32_t in = v[u];
 #pragma unroll
                     for (int d = 1; d < 32; d <<= 1) {
-                        const uint32_t tx = __shfl_up_sync(0xffffffffu, in.x, d), ty = __shfl_up_sync(0xffffffffu, in.y, d);
-                        const uint32_t tz = __shfl_up_sync(0xffffffffu, in.z, d), tw = __shfl_up_sync(0xffffffffu, in.w, d);
-                        if (lane >= d) { in.x += tx; in.y += ty; in.z += tz; in.w += tw; }
+                        const uint32_t t = __shfl_up_sync(0xffffffffu, in, d);
+                        if (lane >= d) in += t;
                     }
-                    if (r < nb)
-                        col[(size_t)r * (TP / 4)] = make_uint4(carry.x + in.x - v[u].x, carry.y + in.y - v[u].y,
-                                                              carry.z + in.z - v[u].z, carry.w + in.w - v[u].w);
-                    carry.x += __shfl_sync(0xffffffffu, in.x, 31); carry.y += __shfl_sync(0xffffffffu, in.y, 31);
-                    carry.z += __shfl_sync(0xffffffffu, in.z, 31); carry.w += __shfl_sync(0xffffffffu, in.w, 31);
+                    if (r < nb) col[(size_t)r * TP] = carry + in - v[u];
+                    carry += __shfl_sync(0xffffffffu, in, 31);
                 }
             }
-            if (lane == 0) reinterpret_cast<uint4 *>(a.tot)[item] = carry;
+            if (lane == 0) a.tot[item] = carry;
         }
     }
     __threadfence();
