@@ -20,6 +20,7 @@
 // ascending-gid order the reference gets from cub (quirk Q2).  All of this is HBM/L2-bound integer work.
 #include "gi2d_common.cuh"
 #include <cooperative_groups.h>
+#include <mutex>
 #include <stdlib.h>
 
 namespace gi2d {
@@ -1160,6 +1161,8 @@ static unsigned int *small_barrier(cudaStream_t stream) {
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 16) return nullptr;
+    static std::mutex init_lock;                      // ctypes releases the GIL: two host threads may get here together
+    std::lock_guard<std::mutex> guard(init_lock);
     if (!pool[dev]) {
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) {
