@@ -132,6 +132,17 @@ class RowShardedRenderer:
         self.render_band(xys, radii, conics, nth, colors, opacity)
         return self.gather()
 
+    def render_compressed_band(self, xyz, quant_cholesky_elements, scale, beta, cholesky_bound, feature_dc_index, codebooks,
+                               opacity) -> torch.Tensor:
+        """Like render_compressed, but WITHOUT the exchange: returns only this rank's band of the frame (rows
+        [rank*band_rows, ...)) -- for consumers that take the frame band by band (per-band encode, display walls)."""
+        from .decode import decode_project_gaussians_2d
+        xys, depths, radii, conics, nth, colors = decode_project_gaussians_2d(
+            xyz, quant_cholesky_elements, scale, beta, cholesky_bound, feature_dc_index, codebooks, self.H, self.W,
+            (self.TX, self.TY, 1))
+        self.render_band(xys, radii, conics, nth, colors, opacity)
+        return self.buffer[self.rank * self.band_rows: (self.rank + 1) * self.band_rows]
+
     def render(self, means2d, L_elements, colors, opacity) -> torch.Tensor:
         """decode step: project all Gaussians (every rank), render own band, all-gather -> (H,W,3) frame."""
         N = means2d.shape[0]
