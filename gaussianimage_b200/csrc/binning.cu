@@ -580,30 +580,49 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
     }
     __syncthreads();
     const unsigned lt = (1u << lane) - 1;
-    // ---- phase 1: per-warp, per-tile counts
-    warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int, int, bool active) {
-        const unsigned peers = __match_any_sync(0xffffffffu, active ? tile : -1 - lane);
-        if (active && (peers & lt) == 0) s_cnt[warp][tile] += (unsigned char)__popc(peers);
-        __syncwarp();
-    });
+    // ---- phase 1: per-warp, per-tile counts.  The first four rounds (128 pairs of the warp) also remember what phase 4
+    // needs -- tile, owner lane and the pair's rank among the warp's pairs of that tile -- so that phase 4 does not walk
+    // and match the pairs a second time: one word per lane and round, bit 31 = valid.
+    uint32_t memo0 = 0, memo1 = 0, memo2 = 0, memo3 = 0;
+    {
+        int round = 0;
+        warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int, int owner, bool active) {
+            const unsigned peers = __match_any_sync(0xffffffffu, active ? tile : -1 - lane);
+            const int rk = __popc(peers & lt);
+            const int before = active ? (int)s_cnt[warp][tile] : 0;
+            __syncwarp();
+            if (active && rk == 0) s_cnt[warp][tile] = (unsigned char)(before + __popc(peers));
+            __syncwarp();
+            const uint32_t v = active ? (0x80000000u | (uint32_t)tile | ((uint32_t)owner << 12) | ((uint32_t)(before + rk) << 17)) : 0u;
+            memo0 = round == 0 ? v : memo0; memo1 = round == 1 ? v : memo1;
+            memo2 = round == 2 ? v : memo2; memo3 = round == 3 ? v : memo3;
+            ++round;
+        });
+    }
     __syncthreads();
     if (a.dbg & 8) return;
-    // ---- phase 2: prefixes over the warps of the block, block totals to the global matrix
-    for (int t = tid; t < TP; t += NT) {
-        int tot = 0;
+    // ---- phase 2: prefixes over the warps of the block, block totals to the global matrix.  Four adjacent tiles per
+    // thread: their byte counters are one 32-bit word per warp row, and the running sums stay packed (a warp adds at most
+    // 32 to a tile, so seven rows stay below 256 per byte); the group totals are widened to 16-bit pairs.
+    {
+        uint32_t *cnt32 = reinterpret_cast<uint32_t *>(s_raw);                         // [SMALL_WARPS][TP / 4]
+        for (int wd = tid; wd < TP / 4; wd += NT) {
+            uint32_t tot_lo = 0, tot_hi = 0;                                           // tiles {0,1} and {2,3} of the word
 #pragma unroll
-        for (int g = 0; g < NGRP; ++g) {
-            s_grp[g][t] = (unsigned short)tot;
-            int run = 0;
+            for (int g = 0; g < NGRP; ++g) {
+                reinterpret_cast<uint2 *>(&s_grp[g][0])[wd] = make_uint2(tot_lo, tot_hi);
+                uint32_t run = 0, c = 0;
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const int c = s_cnt[8 * g + q][t];
-                s_cnt[8 * g + q][t] = (unsigned char)run;  // exclusive inside the group: <= 7 * 32
-                run += c;
+                for (int q = 0; q < 8; ++q) {
+                    c = cnt32[(8 * g + q) * (TP / 4) + wd];
+                    cnt32[(8 * g + q) * (TP / 4) + wd] = run;                          // exclusive inside the group: <= 7 * 32
+                    if (q < 7) run += c;
+                }
+                tot_lo += __byte_perm(run, 0, 0x4140) + __byte_perm(c, 0, 0x4140);
+                tot_hi += __byte_perm(run, 0, 0x4342) + __byte_perm(c, 0, 0x4342);
             }
-            tot += run;
+            reinterpret_cast<uint4 *>(a.mat + (size_t)b * TP)[wd] = make_uint4(tot_lo & 0xffffu, tot_lo >> 16, tot_hi & 0xffffu, tot_hi >> 16);
         }
-        a.mat[(size_t)b * TP + t] = (uint32_t)tot;
     }
     if (a.dbg & 16) return;
     // grid-wide barrier (cooperative launch: all blocks are co-resident, the barrier state belongs to the driver, so
@@ -685,16 +704,7 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
     // ---- phase 4: scatter gid + packed record to the final slot
     const int grp = warp >> 3;
     const float2 rext = record_extent(rcx, rcy, rcz, ro);      // once per Gaussian; every intersection's record carries it
-    warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int gid, int owner, bool active) {
-        const unsigned peers = __match_any_sync(0xffffffffu, active ? tile : -1 - lane);
-        int pos = 0;
-        if (active) {
-            const int before = s_cnt[warp][tile];
-            pos = s_base[tile] + (int)s_grp[grp][tile] + before + __popc(peers & lt);
-        }
-        __syncwarp();
-        if (active && (peers & lt) == 0) s_cnt[warp][tile] += (unsigned char)__popc(peers);
-        __syncwarp();
+    auto emit = [&](int pos, int gid, int owner, bool active) {
         const float x = __shfl_sync(0xffffffffu, rx, owner), y = __shfl_sync(0xffffffffu, ry, owner), o = __shfl_sync(0xffffffffu, ro, owner);
         const float cx = __shfl_sync(0xffffffffu, rcx, owner), cy = __shfl_sync(0xffffffffu, rcy, owner), cz = __shfl_sync(0xffffffffu, rcz, owner);
         const float r = __shfl_sync(0xffffffffu, rr, owner), gg = __shfl_sync(0xffffffffu, rg, owner), bl = __shfl_sync(0xffffffffu, rb, owner);
@@ -705,6 +715,31 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
             __stcs(a.packed + 3 * (size_t)pos + 1, make_float4(cy, cz, r, gg));
             __stcs(a.packed + 3 * (size_t)pos + 2, make_float4(bl, __int_as_float(gid), ex, ey));
         }
+    };
+    const int warp_total = __reduce_add_sync(0xffffffffu, cnt);
+    if (warp_total <= 128) {               // every pair of the warp is in the memo words (warp-uniform branch)
+#pragma unroll
+        for (int round = 0; round < 4; ++round) {
+            if (round * 32 >= warp_total) break;
+            const uint32_t v = round == 0 ? memo0 : round == 1 ? memo1 : round == 2 ? memo2 : memo3;
+            const bool active = (v >> 31) != 0;
+            const int tile = (int)(v & 4095u), owner = (int)((v >> 12) & 31u), rank = (int)((v >> 17) & 63u);
+            const int pos = active ? s_base[tile] + (int)s_grp[grp][tile] + (int)s_cnt[warp][tile] + rank : 0;
+            emit(pos, i - lane + owner, owner, active);
+        }
+        return;
+    }
+    warp_pairs(cnt, x0, w, y0, a.TX, i, [&](int tile, int gid, int owner, bool active) {
+        const unsigned peers = __match_any_sync(0xffffffffu, active ? tile : -1 - lane);
+        int pos = 0;
+        if (active) {
+            const int before = s_cnt[warp][tile];
+            pos = s_base[tile] + (int)s_grp[grp][tile] + before + __popc(peers & lt);
+        }
+        __syncwarp();
+        if (active && (peers & lt) == 0) s_cnt[warp][tile] += (unsigned char)__popc(peers);
+        __syncwarp();
+        emit(pos, gid, owner, active);
     });
 }
 

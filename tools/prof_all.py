@@ -1,6 +1,6 @@
 """Driver for one `ncu --set full --profile-from-start off` capture of EVERY kernel of the path: warm-up iterations run
 unprofiled, then exactly one iteration between cudaProfilerStart/Stop.
-  python tools/prof_all.py c2    fit step (project, bin_small, raster fwd/bwd, project bwd) + loss-epilogue step + Adan step
+  python tools/prof_all.py c2    (or c1 / c3) fit step (project, bin_small, raster fwd/bwd, project bwd) + loss-epilogue step + Adan step
   python tools/prof_all.py c5    8K decode from the compressed representation (decode_project, scatter binning, raster fwd)
 """
 import sys
@@ -16,8 +16,8 @@ from gaussianimage_b200.synth import make_config
 mode = sys.argv[1] if len(sys.argv) > 1 else "c2"
 dev = "cuda:0"
 G.set_sync_free(True)
-if mode == "c2":
-    s = make_config("C2")
+if mode in ("c1", "c2", "c3"):
+    s = make_config(mode.upper())
     d = s.to(dev)
     ps = [torch.nn.Parameter(x.clone()) for x in (d.means2d, d.cholesky, d.colors)]
     opt = Adan(ps, lr=1e-3)
