@@ -629,36 +629,55 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
     // this path needs no zero-initialised memory at all)
     __threadfence();
     if (a.bar) grid_barrier(a.bar, gridDim.x); else cooperative_groups::this_grid().sync();
-    // ---- phase 3a: exclusive scan over the BLOCKS of every tile column, in place.  ONE column per warp, columns dealt
-    // round-robin over the blocks first (every SM takes part; with 4 columns per warp only the first quarter of the grid
-    // worked while the rest waited at the barrier below): up to 160 rows are in flight per pass, 5 per lane.
+    // ---- phase 3a: exclusive scan over the BLOCKS of every tile column, in place.  A warp takes FOUR adjacent columns
+    // (16 bytes of every row) and splits the rows into eight contiguous groups, one per quarter-warp row of lanes: each
+    // lane sums its rows serially (all loads of a batch in flight at once), three shuffles turn the group sums into group
+    // offsets, and the lane writes its rows' exclusive prefixes.  Items are dealt round-robin over the blocks first so
+    // that every SM takes part.  The first batch of rows stays in registers; later batches (large grids) are re-read from L2.
     {
+        constexpr int RB3 = NT == 1024 ? 16 : 19;            // 8 x 19 rows cover a one-block-per-SM grid (148 SMs) in one batch
         const int gwarp = warp * nb + b, nwarps = nb * SMALL_WARPS;
-        for (int item = gwarp; item < TP; item += nwarps) {
-            uint32_t *col = a.mat + item;
-            uint32_t carry = 0;
-            for (int r0 = 0; r0 < nb; r0 += 160) {
-                uint32_t v[5];
+        const int c4 = lane & 3, rgrp = lane >> 2;
+        const int R = (nb + 7) >> 3;
+        const int r_lo = rgrp * R, r_hi = min(nb, r_lo + R);
+        for (int item = gwarp; item < TP / 4; item += nwarps) {
+            uint32_t *col = a.mat + item * 4 + c4;
+            uint32_t v[RB3], sum = 0;
 #pragma unroll
-                for (int u = 0; u < 5; ++u) {
-                    const int r = r0 + 32 * u + lane;
-                    v[u] = r < nb ? __ldcg(col + (size_t)r * TP) : 0u;
-                }
+            for (int u = 0; u < RB3; ++u) v[u] = (r_lo + u < r_hi) ? __ldcg(col + (size_t)(r_lo + u) * TP) : 0u;
 #pragma unroll
-                for (int u = 0; u < 5; ++u) {
-                    if (r0 + 32 * u >= nb) break;
-                    const int r = r0 + 32 * u + lane;
-                    uint32_t in = v[u];
+            for (int u = 0; u < RB3; ++u) sum += v[u];
+            for (int r0 = r_lo + RB3; r0 < r_hi; r0 += RB3) {
+                uint32_t t[RB3];
 #pragma unroll
-                    for (int d = 1; d < 32; d <<= 1) {
-                        const uint32_t t = __shfl_up_sync(0xffffffffu, in, d);
-                        if (lane >= d) in += t;
-                    }
-                    if (r < nb) col[(size_t)r * TP] = carry + in - v[u];
-                    carry += __shfl_sync(0xffffffffu, in, 31);
+                for (int u = 0; u < RB3; ++u) t[u] = (r0 + u < r_hi) ? __ldcg(col + (size_t)(r0 + u) * TP) : 0u;
+#pragma unroll
+                for (int u = 0; u < RB3; ++u) sum += t[u];
+            }
+            uint32_t incl = sum;
+#pragma unroll
+            for (int d = 4; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += t;
+            }
+            const uint32_t total = __shfl_sync(0xffffffffu, incl, 28 + c4);
+            uint32_t run = incl - sum;
+#pragma unroll
+            for (int u = 0; u < RB3; ++u) {
+                if (r_lo + u < r_hi) col[(size_t)(r_lo + u) * TP] = run;
+                run += v[u];
+            }
+            for (int r0 = r_lo + RB3; r0 < r_hi; r0 += RB3) {
+                uint32_t t[RB3];
+#pragma unroll
+                for (int u = 0; u < RB3; ++u) t[u] = (r0 + u < r_hi) ? __ldcg(col + (size_t)(r0 + u) * TP) : 0u;
+#pragma unroll
+                for (int u = 0; u < RB3; ++u) {
+                    if (r0 + u < r_hi) col[(size_t)(r0 + u) * TP] = run;
+                    run += t[u];
                 }
             }
-            if (lane == 0) a.tot[item] = carry;
+            if (rgrp == 0) a.tot[item * 4 + c4] = total;
         }
     }
     __threadfence();
