@@ -4,8 +4,9 @@ Mirror of the reference operator gsplat/gsplat/rasterize_sum.py:14-253 (same nam
 value, gradient contract and Python-level errors).  Two execution paths with identical results:
 
 * fast path (depths produced by one of this package's 2D projections, i.e. known to be all zero): the fused,
-  sync-free chain  memset -> scan+emit+histogram -> onesweep passes -> bin edges+record packing -> TMA-staged
-  rasterizer.  The intersection count never leaves the device inside the chain; in the default *strict* mode it is
+  sync-free chain  gi2d_bin_fused (one cooperative counting-sort kernel up to 4096 tiles; count / scan / scatter /
+  per-tile sort above; scan + onesweep passes as the general fallback -- all ending in tile_bins + packed records)
+  -> TMA-staged rasterizer.  The intersection count never leaves the device inside the chain; in the default *strict* mode it is
   read back once, AFTER everything has been enqueued (so the GPU is never idle waiting for the host, unlike the
   reference's mid-pipeline `.item()`, quirk Q12), to detect workspace overflow and retry.  While a CUDA graph is
   being captured, or after `set_sync_free(True)`, no read-back happens at all.
