@@ -66,6 +66,57 @@ def build(verbose: bool = False) -> Path:
     return LIB_PATH
 
 
+GLUE_PATH = _PKG / "_gi2d_torch.so"
+_glue = False               # False = not looked up yet, None = absent / switched off
+
+
+def build_glue() -> Path:
+    """Compile csrc/torch_glue.cpp (host-only C++: allocation + launch sequences over libgi2d.so, no device code) against
+    this interpreter's torch into gaussianimage_b200/_gi2d_torch.so (in-tree; links libgi2d.so through $ORIGIN)."""
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension as E
+    src = _PKG / "csrc" / "torch_glue.cpp"
+    if GLUE_PATH.exists() and GLUE_PATH.stat().st_mtime >= max(src.stat().st_mtime, LIB_PATH.stat().st_mtime):
+        return GLUE_PATH
+    cuda_home = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    cxx = os.environ.get("CXX", "g++")
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-w", str(src), "-o", str(GLUE_PATH),
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}", "-DTORCH_EXTENSION_NAME=_gi2d_torch",
+           "-DTORCH_API_INCLUDE_EXTENSION_H", f"-I{_PKG.parent / 'include'}", f"-I{sysconfig.get_paths()['include']}",
+           f"-I{cuda_home}/include"]
+    cmd += [f"-I{d}" for d in E.include_paths()]
+    for d in E.library_paths():
+        cmd += [f"-L{d}", f"-Wl,-rpath,{d}"]
+    cmd += ["-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch", "-ltorch_python",
+            f"-L{_PKG}", "-lgi2d", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building _gi2d_torch.so failed:\n" + r.stdout[-4000:] + r.stderr[-4000:])
+    return GLUE_PATH
+
+
+def glue():
+    """The optional C++ host glue module (csrc/torch_glue.cpp), or None: absent, or GI2D_HOST_GLUE=0.  Both host paths
+    drive the same kernels through the same C ABI; this one only shortens the host side of an eager call."""
+    global _glue
+    if _glue is False:
+        _glue = None
+        if os.environ.get("GI2D_HOST_GLUE", "1") != "0" and GLUE_PATH.exists():
+            lib()                                   # libgi2d.so first, by path: the glue's DT_NEEDED then binds to this copy
+            import importlib.util
+
+            import torch  # noqa: F401  (libtorch must be loaded before the extension)
+            spec = importlib.util.spec_from_file_location("gaussianimage_b200._gi2d_torch", str(GLUE_PATH))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            if mod.abi_version() != 1:
+                raise RuntimeError("_gi2d_torch.so was built against another libgi2d ABI")
+            _glue = mod
+    return _glue
+
+
 def lib() -> C.CDLL:
     global _lib
     if _lib is None:

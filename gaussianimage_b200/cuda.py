@@ -12,7 +12,7 @@ from typing import Tuple
 import torch
 from torch import Tensor
 
-from ._lib import check, lib
+from ._lib import check, glue, lib
 
 
 def _chk(x: Tensor, name: str) -> Tensor:
@@ -69,6 +69,9 @@ def _p(x) -> int:
 def project_gaussians_2d_forward(num_points: int, means2d: Tensor, L_elements: Tensor, img_height: int,
                                  img_width: int, tile_bounds: Tuple[int, int, int], clip_thresh: float = 0.01):
     """ext.cpp:16 -> bindings.cu:781-839. Returns (xys, depths, radii, conics, num_tiles_hit)."""
+    T = glue()
+    if T is not None:           # same checks, allocations and launch as below, as one C++ call (csrc/torch_glue.cpp)
+        return T.project_fwd(0, int(num_points), means2d, L_elements, None, img_height, img_width, tile_bounds[0], tile_bounds[1])
     means2d, L = _f32(means2d, "means2d"), _f32(L_elements, "L_elements")
     N, dev = int(num_points), means2d.device
     with _guard(dev):
@@ -87,6 +90,10 @@ def project_gaussians_2d_scale_rot_forward(num_points: int, means2d: Tensor, sca
                                            img_height: int, img_width: int, tile_bounds: Tuple[int, int, int],
                                            clip_thresh: float = 0.01):
     """ext.cpp:18 -> bindings.cu:841-899."""
+    T = glue()
+    if T is not None:
+        return T.project_fwd(1, int(num_points), means2d, scales2d, rotation, img_height, img_width, tile_bounds[0],
+                             tile_bounds[1])
     means2d, scales2d, rotation = _f32(means2d, "means2d"), _f32(scales2d, "scales2d"), _f32(rotation, "rotation")
     N, dev = int(num_points), means2d.device
     with _guard(dev):
@@ -279,6 +286,11 @@ def project_backward_autograd(mode: str, num_points: int, params, img_height: in
                                                  want_cov2d=False)[1:]
         return project_gaussians_2d_scale_rot_backward(N, None, params[0], params[1], img_height, img_width, radii, conics,
                                                        v_xy, None, v_conic, want_cov2d=False)[1:]
+    T = glue()
+    if T is not None:
+        if mode == "cholesky":
+            return T.project_bwd_packed(0, N, params[0], None, img_height, img_width, radii, conics, v_xy)[:2]
+        return T.project_bwd_packed(1, N, params[0], params[1], img_height, img_width, radii, conics, v_xy)
     with _guard(dev):
         v_mean2d = torch.empty((N, 2), dtype=torch.float32, device=dev)
         if mode == "cholesky":

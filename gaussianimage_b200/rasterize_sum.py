@@ -23,7 +23,7 @@ from torch import Tensor
 from torch.autograd import Function
 
 from . import cuda as _C
-from ._lib import check, lib
+from ._lib import check, glue, lib
 from .utils import _depths_known_zero, bin_and_sort_gaussians, compute_cumulative_intersects
 
 _sync_free = os.environ.get("GI2D_SYNC_FREE", "0") == "1"
@@ -145,12 +145,16 @@ class _RasterizeGaussiansSum(Function):
         if ctx.fast:
             tile_bins, packed = ctx.saved_tensors
             dev = packed.device
-            v_out = _C._f32(v_out_img.contiguous(), "v_out_img")
-            with _C._guard(dev):
-                grads = torch.empty((N, 12), dtype=torch.float32, device=dev)     # 48-byte rows: vector reductions
-                check(lib().gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(),
-                                                       v_out.data_ptr(), grads.data_ptr(), _C._stream(dev)),
-                      "rasterize_sum_backward")
+            T = glue()
+            if T is not None:
+                grads = T.raster_bwd_packed(N, H, W, tile_bins, packed, v_out_img.contiguous())
+            else:
+                v_out = _C._f32(v_out_img.contiguous(), "v_out_img")
+                with _C._guard(dev):
+                    grads = torch.empty((N, 12), dtype=torch.float32, device=dev)     # 48-byte rows: vector reductions
+                    check(lib().gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(),
+                                                           v_out.data_ptr(), grads.data_ptr(), _C._stream(dev)),
+                          "rasterize_sum_backward")
             v_xy, v_conic, v_colors, v_opacity = grads[:, 0:2], grads[:, 2:5], grads[:, 5:8], grads[:, 8:9]
         else:
             gids_sorted, tile_bins, xys, conics, colors, opacity, background, final_Ts, final_idx = ctx.saved_tensors
@@ -222,6 +226,14 @@ def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, 
     current stream with an intersection capacity `cap`.  Returns a FusedResult: out_img, final_Ts/final_idx (or None),
     tile_bins (T,2), packed (cap*12), gids_sorted (cap), status (2,) = [n, overflow].  host_slot >= 0 also publishes the
     status to that slot of the pinned host ring."""
+    T = glue() if raster is None else None
+    if T is not None:                      # the same allocations and two launches as one C++ call (csrc/torch_glue.cpp)
+        r = FusedResult()
+        (r.out_img, r.final_Ts, r.final_idx, r.tile_bins, r.packed, r._scratch, r._o_gids, r._o_status) = T.fused_forward(
+            xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap,
+            _host_status.base + 8 * host_slot if host_slot >= 0 else 0, bool(want_aux))
+        r._cap = cap
+        return r
     dev = xys.device
     L = lib()
     N = xys.size(0)

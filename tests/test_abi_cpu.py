@@ -52,3 +52,20 @@ def test_library_is_sm100a_with_tma_and_no_fallback():
     assert "sm_100a" in out and "sm_90" not in out
     sass = subprocess.run(["cuobjdump", "-sass", str(_lib.LIB_PATH)], capture_output=True, text=True).stdout
     assert "UBLKCP" in sass, "the rasterizers must stage their batches with bulk TMA copies"
+
+
+def test_host_glue_loads_binds_the_same_library_and_checks_inputs():
+    """csrc/torch_glue.cpp: host-only C++ over the same C ABI (no compute here: CPU tensors must be refused loudly)."""
+    import torch
+    from gaussianimage_b200 import _lib
+    _lib.build_glue()
+    T = _lib.glue()
+    assert T is not None and T.abi_version() == 1
+    for name in ("project_fwd", "project_bwd_packed", "fused_forward", "raster_bwd_packed"):
+        assert callable(getattr(T, name))
+    mapped = {line.split()[-1] for line in open("/proc/self/maps") if "libgi2d" in line}
+    assert mapped == {str(_lib.LIB_PATH)}, mapped          # one copy of the product library (it owns device-side state)
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        T.project_fwd(0, 4, torch.zeros(4, 2), torch.zeros(4, 3), None, 32, 32, 2, 2)
+    with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+        T.raster_bwd_packed(4, 32, 32, torch.zeros(4, 2, dtype=torch.int32), torch.zeros(48), torch.zeros(32, 32, 3))
