@@ -78,7 +78,8 @@ def build_glue() -> Path:
     import torch
     from torch.utils import cpp_extension as E
     src = _PKG / "csrc" / "torch_glue.cpp"
-    if GLUE_PATH.exists() and GLUE_PATH.stat().st_mtime >= max(src.stat().st_mtime, LIB_PATH.stat().st_mtime):
+    hdr = _PKG.parent / "include" / "gi2d.h"
+    if GLUE_PATH.exists() and GLUE_PATH.stat().st_mtime >= max(src.stat().st_mtime, hdr.stat().st_mtime, LIB_PATH.stat().st_mtime):
         return GLUE_PATH
     cuda_home = os.environ.get("CUDA_HOME", "/usr/local/cuda")
     cxx = os.environ.get("CXX", "g++")
@@ -108,9 +109,15 @@ def glue():
             import importlib.util
 
             import torch  # noqa: F401  (libtorch must be loaded before the extension)
-            spec = importlib.util.spec_from_file_location("gaussianimage_b200._gi2d_torch", str(GLUE_PATH))
-            mod = importlib.util.module_from_spec(spec)
-            spec.loader.exec_module(mod)
+            try:
+                spec = importlib.util.spec_from_file_location("gaussianimage_b200._gi2d_torch", str(GLUE_PATH))
+                mod = importlib.util.module_from_spec(spec)
+                spec.loader.exec_module(mod)
+            except (ImportError, OSError) as e:     # e.g. built against another torch: the ctypes host path runs instead
+                import warnings
+                warnings.warn(f"gi2d: host glue {GLUE_PATH.name} could not be loaded ({e}); using the ctypes host path "
+                              "(same kernels). Rebuild with `python -c 'import __graft_entry__ as g; g.build()'`.")
+                return None
             if mod.abi_version() != 1:
                 raise RuntimeError("_gi2d_torch.so was built against another libgi2d ABI")
             _glue = mod
