@@ -15,6 +15,8 @@ rasterize_gaussians_sum -> MSE loss -> backward to means / Cholesky / colours.  
             FP32-pipe peak at the SM clock observed; `hbm_stages` adds the HBM-bound stages against the measured
             copy bandwidth of MEASURED_PEAKS.json.
   cpu_baseline  the CPU restatement of the same path (oracle/, OpenMP on all host cores) on a bounded sample.
+  cpu_baseline_torch  BASELINE.json configs[0]: pure-PyTorch projection + DENSE per-pixel accumulated sum + autograd on
+            the host cores (oracle/torch_dense_cpu.py), timed on a slice of the Gaussians and scaled (linear in N).
 
 `--impl reference` times the reference path on the host cores only (the reference has no CPU implementation of
 this path beyond fragments of _torch_impl.py; the oracle port IS its CPU restatement -- see DESIGN.md section 7).
@@ -160,6 +162,13 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port",
                              "sample": f"{steps} full {args.workload} steps of {name} (oracle/gi2d_oracle.c, OpenMP)"},
             "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if param != "rs":           # the pure-PyTorch dense path of BASELINE.json configs[0] beside it (oracle/torch_dense_cpu.py)
+        from oracle import torch_dense_cpu as TD
+        n_s = 128 if args.workload == "fit" else 384
+        t_rate, t_dt = TD.timed_sample(scene, "fit" if args.workload == "fit" else "render", n_sample=n_s, chunk=32, threads=cores)
+        line["cpu_baseline_torch"] = {"value": t_rate, "unit": unit, "cores": cores, "kind": "port",
+                                      "sample": f"dense pure-PyTorch path on the first {n_s} of {N} Gaussians over the full image "
+                                                f"in {t_dt:.1f} s, scaled by {N}/{n_s}"}
     print(json.dumps(line), flush=True)
 
 
@@ -630,11 +639,24 @@ def run_b200(args):
                  "(FP32 pipe; the contract's hbm/tensor bounds do not apply to this kernel, see DESIGN.md section 5)",
                  "algorithmic_flops_per_launch": (22.0 if render_only else 54.0) * counts["E"]})
 
-    cpu = None
-    if not args.no_cpu_baseline:
+    cpu = cpu_torch = None
+    if not args.no_cpu_baseline and world == 1:
         rate, k, dt = cpu_rate(scene_cpu, param, "render" if render_only else "fit", seconds=12.0)
         cpu = {"value": rate, "unit": "frames/s" if render_only else UNIT, "cores": os.cpu_count(), "kind": "port",
                "sample": f"{k} full steps of the same workload in {dt:.1f} s (oracle/gi2d_oracle.c, OpenMP, all host threads)"}
+        if param != "rs":
+            # BASELINE.json configs[0] / north_star: "the reference's pure-PyTorch CPU path" -- projection in torch ops with
+            # _torch_impl.compute_cov2d_bounds + DENSE per-pixel accumulated sum + autograd (oracle/torch_dense_cpu.py)
+            from oracle import torch_dense_cpu as TD
+            n_s = 384 if render_only else 128
+            try:
+                t_rate, t_dt = TD.timed_sample(scene_cpu, "render" if render_only else "fit", n_sample=n_s, chunk=32,
+                                               threads=os.cpu_count())
+                cpu_torch = {"value": t_rate, "unit": "frames/s" if render_only else UNIT, "cores": os.cpu_count(), "kind": "port",
+                             "sample": f"dense pure-PyTorch path on the first {n_s} of {N} Gaussians over the full {W}x{H} image in "
+                                       f"{t_dt:.1f} s, scaled by {N}/{n_s} (its cost is linear in N: every Gaussian meets every pixel)"}
+            except Exception as e:                          # noqa: BLE001  (a side baseline must not cost the bench line)
+                cpu_torch = {"value": None, "error": f"{type(e).__name__}: {e}"}
 
     # our kernels per step: project_fwd, binning kernel(s), raster_fwd [, raster_bwd, project_bwd]
     from gaussianimage_b200._lib import lib as _gi2d_lib
@@ -649,7 +671,7 @@ def run_b200(args):
                    "l2": "256 MiB buffer rewritten between timed steps (flush)", "parallelism": f"image-parallel x{world}, no collective",
                    "peaks": peaks_src},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
-        "roofline": roof, "stages": table, "cpu_baseline": cpu,
+        "roofline": roof, "stages": table, "cpu_baseline": cpu, "cpu_baseline_torch": cpu_torch,
         "extras": {"warm_l2_back_to_back_ms_per_step": warm_ms, "warm_l2_iters_per_s": 1e3 / warm_ms,
                    "n_isect_checked": n_isect,
                    "fused_loss_epilogue_ms_per_step": fused_ms, "fused_loss_epilogue_iters_per_s": (1e3 / fused_ms) if fused_ms else None},
