@@ -639,3 +639,19 @@ def test_random_shapes_lists_bins_image_and_gradients(case):
     assert_grad_close(_np(g_L), w["v_L"], "d loss / d L_elements")
     assert_grad_close(_np(g_col), w["v_colors"], "d loss / d colors")
     assert_grad_close(_np(g_op), w["v_opacity"], "d loss / d opacity")
+
+
+# ------------------------------------------------------------------------------- host paths
+def test_ctypes_host_path_passes_the_operator_checks_without_the_glue():
+    """The operators reach the C ABI through the C++ host glue (csrc/torch_glue.cpp) when it is built -- which is what every
+    other test in this file exercises -- and through ctypes + Python-side allocation otherwise.  GI2D_HOST_GLUE=0 selects
+    the latter; it is read once per process, so the operator-level parity tests re-run in a fresh interpreter."""
+    import os
+    import subprocess
+    import sys
+    sel = ("operator_fit_step or forward_bit_exact or zero_intersections or scale_rot_fit_step or python_level_errors or "
+           "three_renders_of_one_projection or general_depth_path")
+    r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_gpu_parity.py", "-q", "-x", "-m", "gpu", "-k", sel,
+                        "-p", "no:cacheprovider"], env={**os.environ, "GI2D_HOST_GLUE": "0"}, capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
