@@ -124,6 +124,20 @@ def glue():
     return _glue
 
 
+_cpp_autograd = os.environ.get("GI2D_CPP_AUTOGRAD", "0") == "1"
+
+
+def cpp_autograd():
+    """The glue module when the operators should run as C++ autograd Functions (csrc/torch_glue.cpp: ProjectFn,
+    RasterFusedFn) instead of Python ones -- opt-in, GI2D_CPP_AUTOGRAD=1 or set_cpp_autograd(True) -- else None."""
+    return glue() if _cpp_autograd else None
+
+
+def set_cpp_autograd(flag: bool) -> None:
+    global _cpp_autograd
+    _cpp_autograd = bool(flag)
+
+
 def lib() -> C.CDLL:
     global _lib
     if _lib is None:

@@ -11,6 +11,7 @@ from torch import Tensor
 from torch.autograd import Function
 
 from . import cuda as _C
+from ._lib import cpp_autograd
 
 
 def _tag_zero_depth(depths: Tensor) -> None:
@@ -32,6 +33,12 @@ def project_gaussians_2d(
     Differentiable w.r.t. means2d and L_elements (through xys and conics); `clip_thresh` is ignored exactly as in
     the reference kernel (quirk Q11).
     """
+    T = cpp_autograd()
+    if T is not None:               # the same operator as a C++ autograd Function (csrc/torch_glue.cpp: ProjectFn)
+        out = T.project_autograd(0, means2d.contiguous(), L_elements.contiguous(), None, img_height, img_width,
+                                 tile_bounds[0], tile_bounds[1])
+        _tag_zero_depth(out[1])
+        return tuple(out)
     return _ProjectGaussians2d.apply(
         means2d.contiguous(), L_elements.contiguous(), img_height, img_width, tile_bounds, clip_thresh
     )

@@ -10,6 +10,7 @@ from torch import Tensor
 from torch.autograd import Function
 
 from . import cuda as _C
+from ._lib import cpp_autograd
 from .project_gaussians_2d import _tag_zero_depth
 
 
@@ -23,6 +24,12 @@ def project_gaussians_2d_scale_rot(
     clip_thresh: float = 0.01,
 ) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
     """Returns (xys, depths, radii, conics, num_tiles_hit); differentiable w.r.t. means2d, scales2d, rotation."""
+    T = cpp_autograd()
+    if T is not None and means2d.shape[-2] >= 1 and means2d.shape[-1] == 2:     # else: the ValueError of the Python Function
+        out = T.project_autograd(1, means2d.contiguous(), scales2d.contiguous(), rotation.contiguous(), img_height, img_width,
+                                 tile_bounds[0], tile_bounds[1])
+        _tag_zero_depth(out[1])
+        return tuple(out)
     return _ProjectGaussians2dScaleRot.apply(
         means2d.contiguous(), scales2d.contiguous(), rotation.contiguous(), img_height, img_width, tile_bounds, clip_thresh
     )

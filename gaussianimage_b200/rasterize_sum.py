@@ -23,7 +23,7 @@ from torch import Tensor
 from torch.autograd import Function
 
 from . import cuda as _C
-from ._lib import check, glue, lib
+from ._lib import check, cpp_autograd, glue, lib
 from .utils import _depths_known_zero, bin_and_sort_gaussians, compute_cumulative_intersects
 
 _sync_free = os.environ.get("GI2D_SYNC_FREE", "0") == "1"
@@ -83,6 +83,14 @@ def rasterize_gaussians_sum(
         raise ValueError("xys must have dimensions (N, 2)")
     if colors.ndimension() != 2:
         raise ValueError("colors must have dimensions (N, D)")
+    T = cpp_autograd()
+    if (T is not None and (BLOCK_H, BLOCK_W) == (16, 16) and colors.shape[-1] == 3 and xys.is_cuda
+            and xys.dtype == torch.float32 and _depths_known_zero(depths)):
+        r = _fused_cpp(T, xys.contiguous(), radii.contiguous(), conics.contiguous(), num_tiles_hit.contiguous(),
+                       colors.contiguous(), opacity.contiguous(), background.contiguous(), int(img_height), int(img_width),
+                       return_alpha)
+        if r is not None:
+            return r
     return _RasterizeGaussiansSum.apply(
         xys.contiguous(), depths.contiguous(), radii.contiguous(), conics.contiguous(), num_tiles_hit.contiguous(),
         colors.contiguous(), opacity.contiguous(), img_height, img_width, BLOCK_H, BLOCK_W, background.contiguous(),
@@ -369,6 +377,61 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
         return r
     ctx.save_for_backward(r.tile_bins, r.packed)
     return r.out_img, r.final_Ts
+
+
+_offsets: dict = {}
+
+
+def _fused_cpp(T, xys, radii, conics, nth, colors, opacity, background, H, W, return_alpha):
+    """_forward_fused with the autograd node in C++ (csrc/torch_glue.cpp: RasterFusedFn): same chain, same strict-mode
+    polling and capacity retry, same memo entry.  Returns None when the binning of these geometry tensors is memoised --
+    the Python Function then re-rasterizes it as before."""
+    global _host_status
+    dev, N = xys.device, xys.size(0)
+    TX, TY = (W + 15) // 16, (H + 15) // 16
+    conics, colors = _C._f32(conics, "conics"), _C._f32(colors, "colors")
+    opacity, background = _C._f32(opacity, "opacity"), _C._f32(background.to(dev), "background")
+    radii, nth = _C._i32(radii, "radii"), _C._i32(nth, "num_tiles_hit")
+    key = (dev.index, N, TX, TY)
+    strict = not (_sync_free or torch.cuda.is_current_stream_capturing())
+    if strict and _host_status is None:
+        _host_status = _HostStatus()
+    gkey = (dev.index, _C._stream(dev))
+    if _memoise:
+        g = _geometry.get(gkey)
+        if g is not None and g.matches(xys, radii, nth, key):
+            return None
+    while True:
+        cap = _capacity.get(key)
+        if cap is None:
+            cap = _capacity[key] = max(4 * N, 1 << 14)
+        slot = _host_status.acquire() if strict else -1
+        out_img, final_Ts, _, tile_bins, packed, scratch = T.raster_fused_autograd(
+            xys, radii, conics, nth, colors, opacity, background, H, W, cap,
+            _host_status.base + 8 * slot if slot >= 0 else 0, bool(return_alpha))
+        okey = (N, H, W, cap)
+        off = _offsets.get(okey)
+        if off is None:
+            off = _offsets[okey] = T.fused_offsets(N, H, W, cap)
+        _last_status[dev.index] = (scratch, off[1], cap, key)
+        n = None
+        if not strict:
+            break
+        n, over = _host_status.wait(slot)
+        if not over:
+            break
+        _capacity[key] = int(n * 1.25) + 1024          # truncated: grow and redo
+    if _memoise:
+        g = _Geometry()
+        g.xys, g.radii, g.nth, g.shape = xys.detach(), radii.detach(), nth.detach(), key
+        g.versions = (xys._version, radii._version, nth._version)
+        keep = FusedResult()
+        keep._scratch, keep._o_gids, keep._o_status, keep._cap, keep.tile_bins = scratch, off[0], off[1], cap, tile_bins
+        g.result, g.cap, g.n_isect = keep, cap, n
+        _geometry[gkey] = g
+    if return_alpha:
+        return out_img, 1 - final_Ts
+    return out_img
 
 
 def _forward_staged(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity, background):

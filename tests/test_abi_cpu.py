@@ -69,3 +69,22 @@ def test_host_glue_loads_binds_the_same_library_and_checks_inputs():
         T.project_fwd(0, 4, torch.zeros(4, 2), torch.zeros(4, 3), None, 32, 32, 2, 2)
     with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
         T.raster_bwd_packed(4, 32, 32, torch.zeros(4, 2, dtype=torch.int32), torch.zeros(48), torch.zeros(32, 32, 3))
+
+
+def test_cpp_autograd_switch_routes_the_operators_and_still_refuses_cpu_tensors():
+    """GI2D_CPP_AUTOGRAD / set_cpp_autograd: the operators as C++ autograd Functions (opt-in).  No compute without a GPU:
+    the route must be taken (the error comes from the C++ input check) and must fail as loudly as the Python one."""
+    import torch
+    import gaussianimage_b200 as G
+    from gaussianimage_b200 import _lib
+    _lib.build_glue()
+    assert _lib.cpp_autograd() is None or _lib._cpp_autograd          # off unless the environment asked for it
+    _lib.set_cpp_autograd(True)
+    try:
+        assert _lib.cpp_autograd() is _lib.glue()
+        with pytest.raises(RuntimeError, match="means2d must be a CUDA tensor"):
+            G.project_gaussians_2d(torch.zeros(4, 2), torch.ones(4, 3), 32, 32, (2, 2, 1))
+        with pytest.raises(RuntimeError, match="means2d must be a CUDA tensor"):
+            G.project_gaussians_2d_scale_rot(torch.zeros(4, 2), torch.ones(4, 2), torch.ones(4, 1), 32, 32, (2, 2, 1))
+    finally:
+        _lib.set_cpp_autograd(False)
