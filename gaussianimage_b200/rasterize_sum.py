@@ -135,10 +135,13 @@ class _RasterizeGaussiansSum(Function):
         ctx.N = xys.size(0)
         fast = _depths_known_zero(depths) and xys.is_cuda and xys.dtype == torch.float32
         ctx.fast = fast
+        global fast_calls, staged_calls
         if fast:
+            fast_calls += 1
             out_img, final_Ts = _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background,
                                                return_alpha)
         else:
+            staged_calls += 1
             out_img, final_Ts = _forward_staged(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity,
                                                 background)
         if return_alpha:
@@ -290,6 +293,13 @@ class _Geometry:
 _geometry: dict = {}
 _memoise = True
 geometry_hits = 0          # how many calls re-used a binning result (tests / bench read it)
+fast_calls = 0             # calls that took the fused chain (depths known to be zero: produced by one of our projections)
+staged_calls = 0           # calls that took the reference's staged sequence (arbitrary depths)
+
+
+def stats() -> dict:
+    """Counters of the operator's dispatch (tests read them): which path the calls took, how often the binning was re-used."""
+    return {"fast_calls": fast_calls, "staged_calls": staged_calls, "geometry_hits": geometry_hits}
 
 
 def set_memoise_binning(flag: bool):
@@ -401,6 +411,8 @@ def _fused_cpp(T, xys, radii, conics, nth, colors, opacity, background, H, W, re
         g = _geometry.get(gkey)
         if g is not None and g.matches(xys, radii, nth, key):
             return None
+    global fast_calls
+    fast_calls += 1
     while True:
         cap = _capacity.get(key)
         if cap is None:

@@ -40,13 +40,36 @@ def assert_image_close(got, want, what, exclude=None):
     assert not bad.any(), f"{what}: {bad.sum()} elements beyond 1e-5 relative, max abs err {err[bad].max():.3e}"
 
 
+GRAD_STATS = []        # (what, share of significant elements that pass only through the absolute floor) -- printed at exit
+
+
 def assert_grad_close(got, want, what):
+    """north_star: gradients within 1e-4 relative.  Sums of hundreds of cancelling fp32 terms cannot meet a pure relative
+    bound on their near-zero results (the reference's own atomicAdd order changes those from run to run), so small-magnitude
+    elements get an absolute floor of 1e-5 * max|want| -- and the floor is kept honest: of the SIGNIFICANT elements
+    (|want| > 1e-3 * max|want|) at least 99.9 % must pass the pure 1e-4 relative test."""
     got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
     scale = np.abs(want).max() + 1e-30
     err = np.abs(got - want)
     tol = GRAD_RTOL * np.abs(want) + 1e-5 * scale   # absolute floor: fp32 sums of hundreds of cancelling terms
     assert (err <= tol).all(), (f"{what}: {(err > tol).sum()} elements beyond 1e-4 relative, "
                                 f"max abs err {err.max():.3e} at scale {scale:.3e}")
+    sig = np.abs(want) > 1e-3 * scale
+    if sig.any():
+        pure = err[sig] <= GRAD_RTOL * np.abs(want[sig])
+        share = 1.0 - pure.mean()
+        GRAD_STATS.append((what, float(share), int(sig.sum())))
+        assert share <= 1e-3, (f"{what}: {100 * share:.3f} % of the {sig.sum()} significant elements pass only through the absolute "
+                               f"floor (limit 0.1 %)")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _report_floor_share():
+    yield
+    if GRAD_STATS:
+        worst = sorted(GRAD_STATS, key=lambda t: -t[1])[:5]
+        print("\n[assert_grad_close] share of significant elements needing the absolute floor, worst five: "
+              + "; ".join(f"{w}: {100 * s:.4f} % of {n}" for w, s, n in worst))
 
 
 SCENES = {
@@ -654,4 +677,23 @@ def test_ctypes_host_path_passes_the_operator_checks_without_the_glue():
     r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_gpu_parity.py", "-q", "-x", "-m", "gpu", "-k", sel,
                         "-p", "no:cacheprovider"], env={**os.environ, "GI2D_HOST_GLUE": "0"}, capture_output=True, text=True,
                        timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_cpp_autograd_functions_pass_the_operator_level_suite():
+    """The two operators as C++ autograd Functions (csrc/torch_glue.cpp: ProjectFn, RasterFusedFn; GI2D_CPP_AUTOGRAD=1):
+    every operator-level parity test of this file, the caller-shaped tests, the loss-epilogue and the graph-fit tests re-run
+    in a fresh interpreter with the switch set (and with GI2D_CPP_AUTOGRAD=0 when C++ is the default), so that BOTH
+    autograd front ends are held to the same bar."""
+    import os
+    import subprocess
+    import sys
+    from gaussianimage_b200 import _lib
+    other = "0" if _lib._cpp_autograd else "1"
+    sel = ("operator_fit_step or forward_bit_exact or zero_intersections or scale_rot_fit_step or python_level_errors or "
+           "three_renders_of_one_projection or general_depth_path or random_shapes or graph_capture or reports_overflow or "
+           "reference_shaped or full_size_C2 or full_size_C3 or loss or fit")
+    r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_gpu_parity.py", "tests/test_gpu_callers.py", "tests/test_gpu_fullsize.py",
+                        "tests/test_gpu_loss.py", "tests/test_gpu_fit.py", "-q", "-x", "-m", "gpu", "-k", sel, "-p", "no:cacheprovider"],
+                       env={**os.environ, "GI2D_CPP_AUTOGRAD": other}, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
