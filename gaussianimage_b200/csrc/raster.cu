@@ -2,63 +2,32 @@
 //
 // Replaces the reference's rasterize_forward_sum (gsplat/gsplat/cuda/csrc/forward.cu:512-627) and
 // rasterize_backward_sum_kernel (backward.cu:696-862) with their torch::zeros fills (bindings.cu:443-451,
-// 752-756).  One CTA of 256 threads per 16x16 tile, like the reference, but:
-//   * the tile's batch (<= 256 intersections, quirk Q1) is ONE contiguous span of 48-byte packed records
-//     (binning.cu: bins_pack_kernel) brought into shared memory by a single bulk TMA copy (cp.async.bulk +
-//     mbarrier expect-tx) -- no per-thread index-indirect gathers, no colour loads from global in the inner loop;
+// 752-756).  The reference runs one CTA of 256 pixel-threads per 16x16 tile with two block barriers per batch; here
+// ONE WARP owns a tile, warps are independent pipelines (persistent grid, no block-wide barrier at all), and:
+//   * the tile's batch (<= 256 intersections, quirk Q1) is a contiguous span of 48-byte packed records
+//     (binning.cu) brought into shared memory in chunks of 64 by bulk TMA copies (cp.async.bulk + mbarrier expect-tx)
+//     into a per-warp ring, one chunk in flight while the previous one is evaluated -- no per-thread index-indirect
+//     gathers, no colour loads from global in the inner loop;
 //   * every pair the reference would reject with `alpha < 1/255` for geometric reasons is culled before it is
 //     evaluated, using a conservative per-Gaussian pixel extent (gi2d_common.cuh: visible_extent).  Culling only
 //     removes pairs the reference rejects, so no output bit changes;
-//   * forward: pixel-parallel, a warp owns an 8x4 pixel block and walks only the records whose extent touches
-//     that block (per-warp compacted index list);
-//   * backward: unit-parallel over the records' visible rectangles -- a thread owns one aligned group of 4 pixels
-//     of one record, partial gradients are combined per record through shared memory with plain stores, and one
-//     set of (vector) reductions per (tile, Gaussian) goes to global memory; no shuffle reductions.  (The sum
-//     rasterizer has no transmittance chain, so the order over pixels is free.)
+//   * forward: a lane owns a 4x2 pixel block and walks, in ascending order, only the records whose rectangle touches
+//     that block (per-lane bit masks built with 12 ballots per 32 records) -- the summation order per pixel is the
+//     reference's, the image is bit-identical;
+//   * backward: unit-parallel over the records' visible rectangles -- a lane owns a contiguous piece of the flattened
+//     (record, row, 4-pixel group) list, partial gradients are combined per record through shared memory with plain
+//     stores, and one set of (vector) reductions per (tile, Gaussian) goes to global memory; no shuffle reductions.
+//     (The sum rasterizer has no transmittance chain, so the order over pixels is free.)
 // Per-pair arithmetic up to the two comparisons is the reference's instruction sequence (gi2d_common.cuh).
-// FP32-pipe bound; no tensor cores (not a dense contraction).
+// FP32-pipe / issue bound; no tensor cores (not a dense contraction).
 #include "gi2d_common.cuh"
 
 namespace gi2d {
-
-constexpr int RB = 256;   // threads per CTA = pixels per tile = max records per tile
 
 struct GatherSrc {        // index-indirect sources of the reference-typed entry points
     const int *gids_sorted;
     const float *xys, *conics, *colors, *opac;
 };
-
-// Stage records [lo, lo+cnt) of the tile into shared memory.  TMA: one bulk copy of cnt*48 bytes.
-template <bool TMA>
-__device__ __forceinline__ void stage_records(float4 *s_rec, uint64_t *bar, const float4 *__restrict__ packed,
-                                              const GatherSrc &src, int lo, int cnt) {
-    const int tid = threadIdx.x;
-    if (TMA) {
-        if (tid == 0) {
-            mbar_init(bar, 1);
-            fence_mbar_init();
-            mbar_expect_tx(bar, (uint32_t)cnt * 48u);
-            tma_load_1d(s_rec, packed + 3 * (size_t)lo, (uint32_t)cnt * 48u, bar);
-        }
-        __syncthreads();          // barrier initialised before anybody polls it
-        mbar_wait(bar, 0);
-    } else {
-        if (tid < cnt) {
-            const int g = __ldg(src.gids_sorted + lo + tid);
-            const float x = __ldg(src.xys + 2 * (size_t)g), y = __ldg(src.xys + 2 * (size_t)g + 1);
-            const float cx = __ldg(src.conics + 3 * (size_t)g), cy = __ldg(src.conics + 3 * (size_t)g + 1),
-                        cz = __ldg(src.conics + 3 * (size_t)g + 2);
-            const float r = __ldg(src.colors + 3 * (size_t)g), gg = __ldg(src.colors + 3 * (size_t)g + 1),
-                        b = __ldg(src.colors + 3 * (size_t)g + 2);
-            const float o = __ldg(src.opac + g);
-            s_rec[3 * tid + 0] = make_float4(x, y, o, cx);
-            s_rec[3 * tid + 1] = make_float4(cy, cz, r, gg);
-            const float2 e = record_extent(cx, cy, cz, o);
-            s_rec[3 * tid + 2] = make_float4(b, __int_as_float(g), e.x, e.y);
-        }
-        __syncthreads();
-    }
-}
 
 // Local (tile-relative, inclusive) pixel rectangle in which the record can pass the alpha test.
 // Returns false for "never visible in this tile".
@@ -81,19 +50,132 @@ __device__ __forceinline__ bool record_rect(const float4 &A, const float4 &C, in
 __device__ __forceinline__ void multimem_st_v4(float *mc, float4 v) {
     asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+__device__ __forceinline__ void multimem_st_v2(float *mc, float2 v) {
+    asm volatile("multimem.st.weak.global.v2.f32 [%0], {%1, %2};" ::"l"(mc), "f"(v.x), "f"(v.y) : "memory");
+}
 __device__ __forceinline__ void multimem_st(float *mc, float v) {
     asm volatile("multimem.st.weak.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
 }
 
-// Forward.  PERSISTENT kernel: a CTA walks the tiles  blockIdx.x, blockIdx.x + gridDim.x, ...  of its range and keeps
-// TWO record stages in shared memory: while tile k is evaluated out of stage (k & 1), the bulk TMA copy of tile
-// k+1's records is already in flight into the other stage (its tile_bins range was fetched one tile earlier still).
-// At 8K (130k sparse tiles) the per-tile chain  range load -> TMA -> evaluate -> store  is latency-bound; the
-// two-deep prefetch takes the first two links off the critical path.
+// Per-warp chunk pipeline shared by both rasterizers.  A warp walks the tiles  first, first + stride, ...  of its range; the
+// records of a tile (<= 256, quirk Q1) arrive in chunks of PIPE_CHUNK by bulk TMA copies (cp.async.bulk + mbarrier
+// expect-tx, SASS UBLKCP) into a ring of PIPE_NST stages that belongs to the warp alone.  The PRODUCER cursor (pk, p_off)
+// runs PIPE_NST chunks ahead of the consumer -- across tile boundaries, skipping empty tiles -- so a copy always has a whole
+// chunk of evaluation to land; tile ranges are fetched one tile ahead of either cursor.  Everything here is warp-uniform;
+// lane 0 issues the copies.  No block-wide barrier is involved.
+constexpr int PIPE_CHUNK = 64;                    // records per chunk (two per lane)
+constexpr int PIPE_NST = 2;                       // chunks in flight per warp
+
+struct ChunkPipe {
+    const int2 *bins2;
+    const float4 *packed;
+    float4 *ring;
+    uint64_t *bars;
+    // Work ITEMS: a tile is 1 << ishift items, dealt to different warps.  Either every item of a tile takes all of the
+    // tile's chunks (forward: the items are the two halves of the tile's pixels; c_first = 0, c_step = 1 chunk) or the items
+    // split the chunk sequence between them (backward: item j takes chunks j, j + c_step, ...; gradients add up in global
+    // memory anyway).  The item stride of a warp is a multiple of the items per tile, so c_first is a constant of the warp.
+    int tile_begin, n_items, stride, lane, ishift, c_first, c_step;
+    int pk, p_off;
+    int2 p_rg, p_nx;
+    uint32_t seq;                                 // chunks consumed so far
+
+    // (lo, cnt <= 256) of the tile of item q; empty tiles may still hold the (INT_MAX, 0) preset of gi2d_bin_fused
+    __device__ __forceinline__ int2 load_range(int q) const {
+        const int2 rg = __ldcg(bins2 + tile_begin + (q >> ishift));
+        const int c = rg.y - rg.x;
+        return make_int2(rg.x, c > 0 && rg.x != 0x7fffffff ? min(c, GI2D_BATCH) : 0);     // Q1: first 256 only
+    }
+    __device__ __forceinline__ void produce(int st) {
+        while (pk < n_items && p_off >= p_rg.y) {          // item exhausted (or empty): move on
+            pk += stride;
+            p_off = c_first;
+            p_rg = p_nx;
+            p_nx = (pk + stride < n_items) ? load_range(pk + stride) : make_int2(0, 0);
+        }
+        if (pk >= n_items) return;
+        const uint32_t bytes = (uint32_t)min(PIPE_CHUNK, p_rg.y - p_off) * 48u;
+        if (lane == 0) {
+            mbar_expect_tx(&bars[st], bytes);
+            tma_load_1d(ring + (size_t)st * PIPE_CHUNK * 3, packed + 3 * (size_t)(p_rg.x + p_off), bytes, &bars[st]);
+        }
+        p_off += c_step;
+    }
+    __device__ __forceinline__ void init(const int *tile_bins, const float4 *packed_, float4 *ring_, uint64_t *bars_, int tile_begin_,
+                                         int n_tiles, int ishift_, bool split_chunks, int first, int stride_, int lane_, bool tma) {
+        bins2 = reinterpret_cast<const int2 *>(tile_bins);
+        packed = packed_; ring = ring_; bars = bars_;
+        tile_begin = tile_begin_; ishift = ishift_; n_items = n_tiles << ishift_; stride = stride_; lane = lane_;
+        c_first = split_chunks ? (first & ((1 << ishift_) - 1)) * PIPE_CHUNK : 0;
+        c_step = split_chunks ? PIPE_CHUNK << ishift_ : PIPE_CHUNK;
+        pk = first; p_off = c_first; seq = 0;
+        p_rg = p_nx = make_int2(0, 0);
+        if (!tma) return;
+        if (lane == 0) {
+#pragma unroll
+            for (int s = 0; s < PIPE_NST; ++s) mbar_init(&bars[s], 1);
+            fence_mbar_init();
+        }
+        __syncwarp();
+        if (pk < n_items) p_rg = load_range(pk);
+        if (pk + stride < n_items) p_nx = load_range(pk + stride);
+#pragma unroll
+        for (int s = 0; s < PIPE_NST; ++s) produce(s);
+    }
+    // stage of the chunk about to be consumed; waits until its copy has landed
+    __device__ __forceinline__ float4 *acquire() {
+        const int st = (int)(seq % PIPE_NST);
+        mbar_wait(&bars[st], (seq / PIPE_NST) & 1u);
+        return ring + (size_t)st * PIPE_CHUNK * 3;
+    }
+    // every lane has left the stage (the caller has just executed __syncwarp): refill it with the chunk PIPE_NST ahead
+    __device__ __forceinline__ void release() {
+        produce((int)(seq % PIPE_NST));
+        ++seq;
+    }
+};
+
+// Index-indirect gather of records [first, first + n) into a stage (the reference-typed entry points, no packed records).
+__device__ __forceinline__ void gather_chunk(float4 *rec, const GatherSrc &src, int first, int n, int lane) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int t = 32 * h + lane;
+        if (t < n) {
+            const int g = __ldg(src.gids_sorted + first + t);
+            const float x = __ldg(src.xys + 2 * (size_t)g), y = __ldg(src.xys + 2 * (size_t)g + 1);
+            const float cx = __ldg(src.conics + 3 * (size_t)g), cy = __ldg(src.conics + 3 * (size_t)g + 1),
+                        cz = __ldg(src.conics + 3 * (size_t)g + 2);
+            const float r = __ldg(src.colors + 3 * (size_t)g), gg = __ldg(src.colors + 3 * (size_t)g + 1),
+                        b = __ldg(src.colors + 3 * (size_t)g + 2);
+            const float o = __ldg(src.opac + g);
+            rec[3 * t + 0] = make_float4(x, y, o, cx);
+            rec[3 * t + 1] = make_float4(cy, cz, r, gg);
+            const float2 e = record_extent(cx, cy, cz, o);
+            rec[3 * t + 2] = make_float4(b, __int_as_float(g), e.x, e.y);
+        }
+    }
+    __syncwarp();
+}
+
+// Forward.  WARP-AUTONOMOUS, persistent: every warp of the grid is an independent tile pipeline -- no block-wide barrier
+// anywhere in the kernel.  Tiles are dealt round-robin to CTAs first (tile k -> CTA k % grid, warp slot (k / grid) % 8), so
+// every SM gets the same number of tiles whatever the tile count.
+//   * lane <-> a 4x2 PIXEL BLOCK of the 16x16 tile (bx = lane & 3, by = lane >> 2): 8 pixels, 24 accumulators in registers;
+//     the column terms (dx, cx*dx, cy*dx) are shared by the two rows and the row terms (dy, dy*(cz*dy)) by the four columns,
+//     so a pair costs 13 FP32-pipe instructions instead of the 18 of a one-pixel thread -- and they are the SAME
+//     operations in the same order as the reference's (gi2d_common.cuh: eval_sigma), only hoisted;
+//   * the tile's records arrive in CHUNKS of 64 by bulk TMA copies into a per-warp ring of FW_NST stages; a chunk is in
+//     flight while the previous one is evaluated, across tile boundaries (the producer cursor runs ahead of the consumer);
+//   * per chunk, lane t derives the visible rectangle of record t and 32+t; 4 + 8 ballots over the column / row block bits
+//     give EVERY lane the 64-bit mask of the records that touch ITS block (the rectangle is a product of a column range
+//     and a row range), and the lane walks only those, in ascending order.  The per-pixel summation order is therefore
+//     the reference's (ascending sorted index, forward.cu:566-614) and the image stays bit-identical, while the culling
+//     granularity drops from 8x4 (59 pixel slots per record at 768x512 / 70k) to 4x2 (34; 21 are inside the rectangle).
+//     Lanes run a common trip count (the warp maximum of the mask populations); a lane without work idles predicated off.
 // Loss epilogue: with LOSS the kernel does not write the image; per pixel it forms what the caller would
 // compute next --  image = clamp(out_img, 0, 1)  (gaussianimage_cholesky.py:84),  F.mse_loss(image, gt)  (utils.py:20-25) --
 // and writes the gradient of that loss w.r.t. out_img,  v_out = 2/(3HW) (image - gt) [0 <= out_img <= 1],  straight into the
-// buffer the backward rasterizer reads.  The squared error is summed per thread over the CTA's tiles, reduced once per
+// buffer the backward rasterizer reads.  The squared error is summed per thread over the warp's tiles, reduced once per
 // CTA, and the last CTA to finish adds the per-CTA partials in index order: a deterministic loss, no atomics on floats.
 struct LossArgs {
     const float *gt;          // target, (3,H,W) planes when gt_chw else (H,W,3)
@@ -106,189 +188,223 @@ struct LossArgs {
     float *loss;              // (1)
 };
 
-template <bool TMA, bool AUX, bool LOSS = false>
-__global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int n_tiles, int *tile_bins,
-                                                        const float4 *__restrict__ packed, GatherSrc src,
-                                                        const int *__restrict__ d_status,
-                                                        const float *__restrict__ background, float *__restrict__ out_img,
-                                                        float *__restrict__ final_Ts, int *__restrict__ final_idx,
-                                                        float *out_mc, int vec_ok, LossArgs la = LossArgs{}) {
-    constexpr int NSTAGE = TMA ? 2 : 1;
-    __shared__ __align__(128) float4 s_rec[NSTAGE][RB * 3];
-    __shared__ __align__(8) uint64_t s_bar[NSTAGE];
-    __shared__ int2 s_range[NSTAGE];
-    __shared__ uint8_t s_mask[RB];
-    __shared__ uint8_t s_list[RB / 32][RB];
-    __shared__ __align__(16) float s_out[GI2D_TILE_PIX * 3];          // output tile staging (its own buffer: no stage is aliased)
+constexpr int FW_WARPS = 8;                       // warps per CTA = independent pipelines per CTA
+constexpr int FW_CHUNK = PIPE_CHUNK;
+constexpr int FW_THREADS = FW_WARPS * 32;
+constexpr size_t FW_SMEM = (size_t)FW_WARPS * PIPE_NST * PIPE_CHUNK * 48 + (size_t)FW_WARPS * PIPE_NST * 8;
 
+// SPLIT = 1: a warp renders a whole tile, a lane a 4x2 pixel block (images with many tiles: 8K decode).
+// SPLIT = 2: a warp renders HALF a tile (8 pixel rows), a lane a 2x2 block; the two halves of a tile go to different
+//            warps (different CTAs), each streaming the tile's records itself -- twice the warps for the fitting images
+//            (768x512 has only 1536 tiles for 148 SMs), the same instruction count (finer culling pays for the second
+//            set of masks).
+template <bool TMA, bool AUX, bool LOSS, int SPLIT>
+__global__ void __launch_bounds__(FW_THREADS) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int n_tiles, int *tile_bins,
+                                                                const float4 *__restrict__ packed, GatherSrc src,
+                                                                const int *__restrict__ d_status,
+                                                                const float *__restrict__ background, float *__restrict__ out_img,
+                                                                float *__restrict__ final_Ts, int *__restrict__ final_idx,
+                                                                float *out_mc, int vec_ok, LossArgs la = LossArgs{}) {
+    constexpr int ISHIFT = SPLIT == 2 ? 1 : 0;
+    constexpr int BW = 4 / SPLIT;                         // pixels per lane and row
+    constexpr int XSH = SPLIT == 2 ? 1 : 2;               // log2(BW)
+    constexpr int NBX = GI2D_TILE / BW, NBY = 8 / SPLIT;  // lane blocks across / down the warp's part of the tile (NBX * NBY = 32)
+    constexpr int ROWS = GI2D_TILE / SPLIT;               // pixel rows of the warp's part
+    extern __shared__ __align__(128) unsigned char fw_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int stride = gridDim.x;
-    int k = blockIdx.x;                                   // index of the current tile inside [0, n_tiles)
-    if (k >= n_tiles) return;
-    int2 *bins2 = reinterpret_cast<int2 *>(tile_bins);
-    // warp -> 8x4 pixel block (2 across, 4 down); lane -> pixel inside it
-    const int bx = warp & 1, by = warp >> 1;
+    const int G = gridDim.x, stride = G * FW_WARPS;
+    const int bxm = lane % NBX, bym = lane / NBX;         // this lane's pixel block
+    const bool none_at_all = d_status && background && __ldg(d_status) == 0;   // rasterize_sum.py:121-129
+    const int first = warp * G + blockIdx.x, n_items = n_tiles << ISHIFT;
+    ChunkPipe pipe;
+    pipe.init(tile_bins, packed, reinterpret_cast<float4 *>(fw_smem) + (size_t)warp * PIPE_NST * PIPE_CHUNK * 3,
+              reinterpret_cast<uint64_t *>(fw_smem + (size_t)FW_WARPS * PIPE_NST * PIPE_CHUNK * 48) + warp * PIPE_NST, tile_begin, n_tiles,
+              ISHIFT, false, first, stride, lane, TMA);
+    const int part = first & (SPLIT - 1);                 // which half of its tiles this warp renders (constant: stride is even)
 
-    // thread 0 is the producer: fetches ranges two tiles ahead, issues the TMA copy one tile ahead
-    auto fetch_range = [&](int kk) -> int2 {
-        int2 rg = bins2[tile_begin + kk];
-        if (rg.x == 0x7fffffff) {                         // empty tile left at (INT_MAX, 0) by gi2d_bin_fused:
-            rg = make_int2(0, 0);                         // canonical (0, 0) like the reference's zero fill
-            bins2[tile_begin + kk] = rg;
-        }
-        return rg;
-    };
-    auto issue = [&](int st, int2 rg) {
-        s_range[st] = rg;
-        const int c = min(rg.y - rg.x, GI2D_BATCH);
-        if (c > 0) {
-            mbar_expect_tx(&s_bar[st], (uint32_t)c * 48u);
-            tma_load_1d(s_rec[st], packed + 3 * (size_t)rg.x, (uint32_t)c * 48u, &s_bar[st]);
-        }
-    };
-    // Barriers per tile: ONE after the culling masks and ONE after the output tile is staged.  The second one also says
-    // "every warp has left the evaluation loop", i.e. the tile's record stage is free: thread 0 re-arms it right there
-    // with the copy for the tile after next, so a copy always has a whole tile of evaluation to land.
-    int2 r_next = make_int2(0, 0);
-    if (TMA) {
-        if (tid == 0) {
-            mbar_init(&s_bar[0], 1);
-            mbar_init(&s_bar[NSTAGE - 1], 1);
-            fence_mbar_init();
-            issue(0, fetch_range(k));
-            if (k + stride < n_tiles) issue(NSTAGE - 1, fetch_range(k + stride));
-            if (k + 2 * stride < n_tiles) r_next = fetch_range(k + 2 * stride);
-        }
-        __syncthreads();                                  // barrier initialisation and s_range[] visible
-    }
-    uint32_t phase_bits = 0;                              // bit st = parity of the next completion of s_bar[st]
-    float sq_sum = 0.f;                                   // LOSS: this thread's share of the squared error
-
-    // tile coordinates advance by (stride / TX, stride % TX) per iteration: no division inside the loop
-    const int step_y = stride / TX, step_x = stride - step_y * TX;
-    int ty = (tile_begin + k) / TX, tx = (tile_begin + k) - ty * TX;
-    for (int it = 0; k < n_tiles; k += stride, ++it, tx += step_x, ty += step_y) {
-        const int st = TMA ? (it & 1) : 0;
-        if (!TMA) {
-            if (tid == 0) s_range[0] = bins2[tile_begin + k];
-            __syncthreads();
-        }
-        if (tx >= TX) { tx -= TX; ++ty; }
+    float sq_sum = 0.f;                                    // LOSS: this thread's share of the squared error
+    int q = first;
+    int2 c_nx = q < n_items ? pipe.load_range(q) : make_int2(0, 0);
+    for (; q < n_items; q += stride) {
+        const int2 rg = c_nx;
+        if (q + stride < n_items) c_nx = pipe.load_range(q + stride);
+        const int tile = tile_begin + (q >> ISHIFT);
+        const int ty = tile / TX, tx = tile - ty * TX;
         const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
-        const int j = tx0 + bx * 8 + (lane & 7), i = ty0 + by * 4 + (lane >> 3);
-        const bool inside = i < H && j < W;
-        const size_t pix = (size_t)i * W + j;
-        const int2 range = s_range[st];
-        const int lo = range.x;
-        const int cnt = min(range.y - range.x, GI2D_BATCH);          // Q1: only the first 256 sorted intersections count
-        const float4 *rec = s_rec[st];
+        const int lo = rg.x, cnt = rg.y;
+        if (TMA && cnt == 0 && lane == 0 && part == 0) reinterpret_cast<int2 *>(tile_bins)[tile] = make_int2(0, 0);   // canonical (0, 0) like the reference's zero fill
+        const int row0 = ROWS * part;                      // first tile row of this warp's part
+        const float pxf = (float)(tx0 + BW * bxm), pyf = (float)(ty0 + row0 + 2 * bym);
 
-        float r = 0.f, g = 0.f, b = 0.f, T_final = 1.f;   // T is never updated in the sum rasterizer (Q6)
-        int cur = 0;
-        if (cnt > 0) {
-            if (TMA) {
-                mbar_wait(&s_bar[st], (phase_bits >> st) & 1u);
-                phase_bits ^= 1u << st;
-            } else {
-                stage_records<false>(s_rec[0], &s_bar[0], packed, src, lo, cnt);
-            }
-            if (tid < cnt) {
-                int lx0, lx1, ly0, ly1;
-                uint32_t m = 0;
-                if (record_rect(rec[3 * tid], rec[3 * tid + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
-                    const uint32_t colm = (lx0 <= 7 ? 1u : 0u) | (lx1 >= 8 ? 2u : 0u);      // which 8-wide halves
+        float acc[2][BW][3];
+        int cur[2][BW];
 #pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        if (ly0 <= 4 * q + 3 && ly1 >= 4 * q) m |= colm << (2 * q);       // bit = by*2 + bx
+        for (int r = 0; r < 2; ++r)
+#pragma unroll
+            for (int c = 0; c < BW; ++c) {
+                acc[r][c][0] = acc[r][c][1] = acc[r][c][2] = 0.f;
+                cur[r][c] = 0;
+            }
+        float T_final = 1.f;                               // T is never updated in the sum rasterizer (Q6)
+
+        for (int off = 0; off < cnt; off += FW_CHUNK) {
+            const int n = min(FW_CHUNK, cnt - off);
+            float4 *rec;
+            if (TMA) {
+                rec = pipe.acquire();
+            } else {                                       // reference-typed entry: index-indirect gather by the warp itself
+                rec = pipe.ring;
+                gather_chunk(rec, src, lo + off, n, lane);
+            }
+            // which records of the chunk touch this lane's pixel block: 64-bit mask from 2 x (NBX + NBY = 12) ballots
+            uint32_t m[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int t = 32 * h + lane;
+                uint32_t colbits = 0, rowbits = 0;
+                if (t < n) {
+                    int lx0, lx1, ly0, ly1;
+                    if (record_rect(rec[3 * t], rec[3 * t + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
+                        const int r0 = max(ly0, row0) - row0, r1 = min(ly1, row0 + ROWS - 1) - row0;
+                        if (r0 <= r1) {
+                            colbits = (2u << (lx1 >> XSH)) - (1u << (lx0 >> XSH));
+                            rowbits = (2u << (r1 >> 1)) - (1u << (r0 >> 1));
+                        }
+                    }
                 }
-                s_mask[tid] = (uint8_t)m;
+                uint32_t myC = 0, myR = 0;
+#pragma unroll
+                for (int j = 0; j < NBX; ++j) {
+                    const uint32_t b = __ballot_sync(0xffffffffu, (colbits >> j) & 1u);
+                    myC = bxm == j ? b : myC;
+                }
+#pragma unroll
+                for (int j = 0; j < NBY; ++j) {
+                    const uint32_t b = __ballot_sync(0xffffffffu, (rowbits >> j) & 1u);
+                    myR = bym == j ? b : myR;
+                }
+                m[h] = myC & myR;
             }
-        }
-        __syncthreads();             // masks visible; also: the previous tile's readers of s_out are done (empty tiles included)
-        if (cnt > 0) {
-            // per-warp compaction of the record indices whose extent touches this warp's pixel block
-            int nlist = 0;
-            for (int c = 0; c < cnt; c += 32) {
-                const int t = c + lane;
-                const bool hit = t < cnt && ((s_mask[t] >> warp) & 1);
-                const unsigned bal = __ballot_sync(0xffffffffu, hit);
-                if (hit) s_list[warp][nlist + __popc(bal & ((1u << lane) - 1))] = (uint8_t)t;
-                nlist += __popc(bal);
-            }
-            __syncwarp();
-            const float px = (float)j, py = (float)i;
-            for (int q = 0; q < nlist; ++q) {
-                const int t = s_list[warp][q];
+            const int n_it = __reduce_max_sync(0xffffffffu, __popc(m[0]) + __popc(m[1]));
+            const int idx0 = lo + off;
+            for (int it = 0; it < n_it; ++it) {
+                const bool h0 = m[0] != 0u;
+                uint32_t mm = h0 ? m[0] : m[1];
+                const bool act = mm != 0u;
+                const int t = act ? (__ffs((int)mm) - 1 + (h0 ? 0 : 32)) : 0;
+                mm &= mm - 1u;
+                if (h0) m[0] = mm; else m[1] = mm;
                 const float4 A = rec[3 * t], B = rec[3 * t + 1];
-                const float dx = fsub(A.x, px), dy = fsub(A.y, py);
-                const float sigma = eval_sigma(dx, dy, A.w, B.x, B.y);
-                const float alpha = fminf(fmul(A.z, exp_neg(sigma)), 1.f);
-                if (sigma < 0.f || alpha < GI2D_ALPHA_MIN) continue;          // forward.cu:602-604
                 const float cb = rec[3 * t + 2].x;
-                r = ffma(alpha, B.z, r);                                       // forward.cu:607-609
-                g = ffma(alpha, B.w, g);
-                b = ffma(alpha, cb, b);
-                cur = lo + t;                                                  // forward.cu:611
-            }
-        } else if (d_status && background && __ldg(d_status) == 0) {
-            // no intersections at all: rasterize_sum.py:121-129 returns ones * background
-            r = __ldg(background); g = __ldg(background + 1); b = __ldg(background + 2);
-            T_final = 0.f;                  // ... and final_Ts = zeros there (rasterize_sum.py:128)
-        }
-        // Epilogue.  A tile that lies fully inside the image leaves as 16 rows x 12 float4 (one 192-byte run per row)
-        // staged through shared memory; with `out_mc` (the NVLS multicast alias of a symmetric frame buffer) every store
-        // is a `multimem.st`, which the NVSwitch replicates into the frame buffer of EVERY rank -- the all-gather of a
-        // row-sharded render happens inside the rasterizer.
-        if (LOSS) {
-            float cr = r, cg = g, cb = b;
-            if (la.clamp) { cr = fminf(fmaxf(r, 0.f), 1.f); cg = fminf(fmaxf(g, 0.f), 1.f); cb = fminf(fmaxf(b, 0.f), 1.f); }
-            float dr = 0.f, dg = 0.f, db = 0.f;
-            if (inside) {
-                if (la.gt_chw) {
-                    const size_t plane = (size_t)H * W;
-                    dr = cr - __ldg(la.gt + pix); dg = cg - __ldg(la.gt + plane + pix); db = cb - __ldg(la.gt + 2 * plane + pix);
-                } else {
-                    dr = cr - __ldg(la.gt + 3 * pix); dg = cg - __ldg(la.gt + 3 * pix + 1); db = cb - __ldg(la.gt + 3 * pix + 2);
+                float dx[BW], u[BW], w[BW];
+#pragma unroll
+                for (int c = 0; c < BW; ++c) {
+                    dx[c] = fsub(A.x, pxf + (float)c);
+                    u[c] = fmul(A.w, dx[c]);                // cx * dx
+                    w[c] = fmul(B.x, dx[c]);                // cy * dx
                 }
-                sq_sum += dr * dr + dg * dg + db * db;
-                if (la.image) { la.image[3 * pix] = cr; la.image[3 * pix + 1] = cg; la.image[3 * pix + 2] = cb; }
+#pragma unroll
+                for (int r = 0; r < 2; ++r) {
+                    const float dy = fsub(A.y, pyf + (float)r);
+                    const float t3 = fmul(dy, fmul(B.y, dy));                          // dy * (cz * dy)
+#pragma unroll
+                    for (int c = 0; c < BW; ++c) {
+                        const float qq = ffma(dx[c], u[c], t3);                         // eval_sigma, hoisted
+                        const float sigma = ffma(dy, w[c], fmul(qq, 0.5f));
+                        const float alpha = fminf(fmul(A.z, exp_neg(sigma)), 1.f);
+                        if (act && !(sigma < 0.f) && !(alpha < GI2D_ALPHA_MIN)) {      // forward.cu:602-604
+                            acc[r][c][0] = ffma(alpha, B.z, acc[r][c][0]);             // forward.cu:607-609
+                            acc[r][c][1] = ffma(alpha, B.w, acc[r][c][1]);
+                            acc[r][c][2] = ffma(alpha, cb, acc[r][c][2]);
+                            if (AUX) cur[r][c] = idx0 + t;                              // forward.cu:611
+                        }
+                    }
+                }
             }
-            const float sc = 2.f * la.inv_numel;
-            // torch.clamp passes the gradient where min <= x <= max
-            r = (!la.clamp || (r >= 0.f && r <= 1.f)) ? sc * dr : 0.f;
-            g = (!la.clamp || (g >= 0.f && g <= 1.f)) ? sc * dg : 0.f;
-            b = (!la.clamp || (b >= 0.f && b <= 1.f)) ? sc * db : 0.f;
+            __syncwarp();                                  // every lane has left the stage
+            if (TMA) pipe.release();                       // refill it with the chunk PIPE_NST ahead
         }
+        if (cnt == 0 && none_at_all) {                     // no intersections at all: ones * background, final_Ts = zeros
+            const float b0 = __ldg(background), b1 = __ldg(background + 1), b2 = __ldg(background + 2);
+#pragma unroll
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+                for (int c = 0; c < BW; ++c) { acc[r][c][0] = b0; acc[r][c][1] = b1; acc[r][c][2] = b2; }
+            T_final = 0.f;
+        }
+        // ---- epilogue: the lane owns BW consecutive pixels of two rows = two runs of 12 * BW contiguous bytes.  With `out_mc`
+        // (the NVLS multicast alias of a symmetric frame buffer) every store is a `multimem.st`, which the NVSwitch replicates
+        // into the frame buffer of EVERY rank -- the all-gather of a row-sharded render happens inside the rasterizer.
         float *const dst_img = LOSS ? la.v_out : out_img;
-        const bool vec_tile = vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H;     // uniform over the CTA
-        if (vec_tile) {
-            const int lp = (by * 4 + (lane >> 3)) * GI2D_TILE + bx * 8 + (lane & 7);
-            s_out[3 * lp] = r; s_out[3 * lp + 1] = g; s_out[3 * lp + 2] = b;
-        }
-        __syncthreads();             // output tile staged; every warp has left its loop: stage st, s_mask, s_list are free
-        if (TMA && tid == 0 && k + 2 * stride < n_tiles) {
-            issue(st, r_next);                                                  // tile after next, into the stage just left
-            if (k + 3 * stride < n_tiles) r_next = fetch_range(k + 3 * stride);
-        }
-        if (vec_tile) {
-            if (tid < 192) {
-                const int row = tid / 12, q = tid - row * 12;
-                const float4 v = reinterpret_cast<const float4 *>(s_out)[tid];
-                const size_t off = ((size_t)(ty0 + row) * W + tx0) * 3 + 4 * q;
-                if (out_mc) multimem_st_v4(out_mc + off, v);
-                else *reinterpret_cast<float4 *>(dst_img + off) = v;
+        const bool vec_tile = vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H;     // uniform over the warp
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const int i = ty0 + row0 + 2 * bym + r, j0 = tx0 + BW * bxm;
+            const size_t pix0 = (size_t)i * W + j0;
+            float v[3 * BW];
+#pragma unroll
+            for (int c = 0; c < BW; ++c) { v[3 * c] = acc[r][c][0]; v[3 * c + 1] = acc[r][c][1]; v[3 * c + 2] = acc[r][c][2]; }
+            if (LOSS) {
+                const float sc = 2.f * la.inv_numel;
+                const size_t plane = (size_t)H * W;
+#pragma unroll
+                for (int c = 0; c < BW; ++c) {
+                    const bool inside = i < H && j0 + c < W;
+#pragma unroll
+                    for (int ch = 0; ch < 3; ++ch) {
+                        const float raw = v[3 * c + ch];
+                        const float cl = la.clamp ? fminf(fmaxf(raw, 0.f), 1.f) : raw;
+                        float d = 0.f;
+                        if (inside) {
+                            const float g = la.gt_chw ? __ldg(la.gt + ch * plane + pix0 + c) : __ldg(la.gt + 3 * (pix0 + c) + ch);
+                            d = cl - g;
+                            if (la.image) la.image[3 * (pix0 + c) + ch] = cl;
+                        }
+                        sq_sum += d * d;
+                        // torch.clamp passes the gradient where min <= x <= max
+                        v[3 * c + ch] = (!la.clamp || (raw >= 0.f && raw <= 1.f)) ? sc * d : 0.f;
+                    }
+                }
             }
-        } else if (inside) {
-            if (out_mc) { multimem_st(out_mc + 3 * pix, r); multimem_st(out_mc + 3 * pix + 1, g); multimem_st(out_mc + 3 * pix + 2, b); }
-            else { dst_img[3 * pix] = r; dst_img[3 * pix + 1] = g; dst_img[3 * pix + 2] = b; }
-        }
-        if (AUX && inside) {
-            final_Ts[pix] = T_final;
-            final_idx[pix] = cur;
+            if (vec_tile) {
+                if (BW == 4) {
+#pragma unroll
+                    for (int k4 = 0; k4 < 3; ++k4) {
+                        const float4 o4 = make_float4(v[4 * k4], v[4 * k4 + 1], v[4 * k4 + 2], v[4 * k4 + 3]);
+                        if (out_mc) multimem_st_v4(out_mc + 3 * pix0 + 4 * k4, o4);
+                        else *reinterpret_cast<float4 *>(dst_img + 3 * pix0 + 4 * k4) = o4;
+                    }
+                } else {                                   // 2 pixels = 24 contiguous bytes, 8-byte aligned
+#pragma unroll
+                    for (int k2 = 0; k2 < 3; ++k2) {
+                        const float2 o2 = make_float2(v[2 * k2], v[2 * k2 + 1]);
+                        if (out_mc) multimem_st_v2(out_mc + 3 * pix0 + 2 * k2, o2);
+                        else *reinterpret_cast<float2 *>(dst_img + 3 * pix0 + 2 * k2) = o2;
+                    }
+                }
+            } else if (i < H) {
+#pragma unroll
+                for (int c = 0; c < BW; ++c)
+                    if (j0 + c < W) {
+#pragma unroll
+                        for (int ch = 0; ch < 3; ++ch) {
+                            if (out_mc) multimem_st(out_mc + 3 * (pix0 + c) + ch, v[3 * c + ch]);
+                            else dst_img[3 * (pix0 + c) + ch] = v[3 * c + ch];
+                        }
+                    }
+            }
+            if (AUX && i < H) {
+#pragma unroll
+                for (int c = 0; c < BW; ++c)
+                    if (j0 + c < W) {
+                        final_Ts[pix0 + c] = T_final;
+                        final_idx[pix0 + c] = cur[r][c];
+                    }
+            }
         }
     }
     if (LOSS) {
-        __shared__ float s_red[RB / 32];
+        __shared__ float s_red[FW_WARPS];
         __shared__ bool s_last;
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) sq_sum += __shfl_xor_sync(0xffffffffu, sq_sum, d);
@@ -297,7 +413,7 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
         if (tid == 0) {
             float t = 0.f;
 #pragma unroll
-            for (int w = 0; w < RB / 32; ++w) t += s_red[w];
+            for (int w = 0; w < FW_WARPS; ++w) t += s_red[w];
             la.partials[blockIdx.x] = t;
             __threadfence();
             s_last = atomicAdd(la.ticket, 1u) == gridDim.x - 1;
@@ -317,17 +433,18 @@ __global__ void __launch_bounds__(RB) raster_fwd_kernel(int TX, int W, int H, in
     }
 }
 
-// Backward.  Work unit = one ALIGNED GROUP OF 4 PIXELS of one row of one staged record's visible rectangle.  The units
-// of all records of the tile form one flattened list (record-major, row-major inside a record); thread t owns the
-// CONTIGUOUS chunk [t*R, t*R+R) of it (R = ceil(units/256)), so every lane has the same number of four-pixel
-// evaluations whatever the records' footprints are, and a thread's consecutive units mostly belong to one record:
-// its partial sums stay in registers and are flushed only when the chunk crosses into the next record -- with nine
-// PLAIN shared-memory stores into slot (thread + record): along the flattened list the (thread, record) pairs form a
-// monotone staircase, so that sum is unique per flush (shared-memory float atomics are CAS loops on sm_100).  No
-// barrier inside the main loop, no shuffle reductions, no shared atomics; after one final barrier the thread that
-// staged record t adds up the slots of the threads [pref[t]/R, (pref[t+1]-1)/R] whose chunks intersect it, turns the
-// sums into the nine gradients and issues ONE set of global reductions per (tile, Gaussian): three 16-byte
-// `red.global.add.v4.f32` in the packed layout.
+// Backward.  WARP-AUTONOMOUS like the forward: a warp takes a tile's records in chunks of 64 through the same TMA ring, and
+// no block-wide barrier exists.  Work unit = one ALIGNED 4x2 PIXEL BLOCK touched by one staged record's visible
+// rectangle (column terms shared by the two rows, row terms by the four columns, as in the forward).  The units of all
+// records of a chunk form one flattened list (record-major, row-major inside a record); lane l owns the CONTIGUOUS piece
+// [l*R, l*R+R) of it (R = ceil(units/32)), so every lane has the same number of eight-pixel evaluations whatever the
+// records' footprints are, and a lane's consecutive units mostly belong to one record: its partial sums stay in registers
+// and are flushed only when the piece crosses into the next record -- with nine PLAIN shared-memory stores into slot
+// (lane + record): along the flattened list the (lane, record) pairs form a monotone staircase, so that sum is unique per
+// flush (shared-memory float atomics are CAS loops on sm_100: `ATOMS.CAST.SPIN`).  No shuffle reductions, no shared
+// atomics; after a __syncwarp the lane that staged record t adds up the slots of the lanes [pref[t]/R, (pref[t+1]-1)/R]
+// whose pieces intersect it, turns the sums into the nine gradients and issues ONE set of global reductions per
+// (tile chunk, Gaussian): two 16-byte `red.global.add.v4.f32` + one scalar in the packed layout.
 //
 // Sums kept per record (m = vis * v_alpha for a contributing pixel, 0 otherwise; dx, dy as in backward.cu:797-799):
 //   S_m = sum m, S_x = sum m dx, S_y = sum m dy, S_xx = sum m dx dx, S_xy = sum m dx dy, S_yy = sum m dy dy, and
@@ -343,180 +460,216 @@ struct GradOut {            // VEC12: g12 = (N,12) rows {v_xy.x, v_xy.y, v_conic
     float *v_xy, *v_conic, *v_colors, *v_opacity;
 };
 
+constexpr int BW_WARPS = 8;
+constexpr int BW_THREADS = BW_WARPS * 32;
+struct __align__(16) BwdWarpSmem {
+    float4 ring[PIPE_NST][PIPE_CHUNK * 3];        // staged records
+    float v[3][GI2D_TILE_PIX];                    // upstream gradient of the tile, one plane per channel
+    uint16_t pref[PIPE_CHUNK + 2];                // exclusive prefix of the unit counts; [PIPE_CHUNK] = total
+    uint8_t rect[PIPE_CHUNK];                     // bx0 | nbx<<2 | by0<<5: the 4x2 pixel blocks a record's rectangle touches
+    uint64_t bars[PIPE_NST];
+};
+constexpr size_t BW_SMEM = sizeof(BwdWarpSmem) * BW_WARPS;
+
+// ishift: a tile is 1 << ishift work items (warps); item j of a tile takes its chunks j, j + (1 << ishift), ... -- the per-record
+// sums of different chunks are independent and the gradients meet in global memory, so the split needs no communication;
+// it doubles / quadruples the warps in flight for the fitting images, whose 1536-2752 tiles do not fill 148 SMs.
 template <bool TMA, bool VEC12>
-__global__ void __launch_bounds__(RB) raster_bwd_kernel(int TX, int W, int H, const int *__restrict__ tile_bins,
-                                                        const float4 *__restrict__ packed, GatherSrc src,
-                                                        const float *__restrict__ v_out, GradOut out,
-                                                        const float *__restrict__ v_scale = nullptr) {
-    __shared__ __align__(128) float4 s_rec[RB * 3];
-    __shared__ __align__(16) float s_v[3][GI2D_TILE_PIX];      // upstream gradient, one plane per channel
-    __shared__ float s_part[9][2 * RB];                        // flushed partial sums, slot = thread + record
-    __shared__ uint32_t s_rect[RB];                            // x0 | x1<<4 | y0<<8 | g0<<12 | segs<<14 | rows<<17
-    __shared__ uint16_t s_pref[RB + 1];                        // exclusive prefix of the unit counts; [RB] = total
-    __shared__ int s_warp[RB / 32];
-    __shared__ __align__(8) uint64_t s_bar;
-
+__global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W, int H, int n_tiles, int ishift, const int *__restrict__ tile_bins,
+                                                                const float4 *__restrict__ packed, GatherSrc src,
+                                                                const float *__restrict__ v_out, GradOut out, int vec_ok,
+                                                                const float *__restrict__ v_scale = nullptr) {
+    extern __shared__ __align__(128) unsigned char bw_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
-    const int ty = tile / TX, tx = tile - ty * TX;
-    const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
-    const int2 range = __ldg(reinterpret_cast<const int2 *>(tile_bins) + tile);
-    const int lo = range.x;
-    const int cnt = min(range.y - range.x, GI2D_BATCH);
-    if (cnt <= 0) return;
+    BwdWarpSmem &S = reinterpret_cast<BwdWarpSmem *>(bw_smem)[warp];
+    const int G = gridDim.x, stride = G * BW_WARPS;
+    ChunkPipe pipe;
+    const int first = warp * G + blockIdx.x, n_items = n_tiles << ishift;
+    pipe.init(tile_bins, packed, &S.ring[0][0], S.bars, 0, n_tiles, ishift, true, first, stride, lane, TMA);
+    const float vsc = v_scale ? __ldg(v_scale) : 1.f;     // upstream gradient of a scalar loss whose d/d out_img is already in v_out
 
-    {   // the tile of upstream gradients, zero outside the image (such pixels then contribute exact zeros)
-        const int j = tx0 + (tid & 15), i = ty0 + (tid >> 4);
-        float vr = 0.f, vg = 0.f, vb = 0.f;
-        if (i < H && j < W) {
-            const size_t pix = (size_t)i * W + j;
-            vr = __ldg(v_out + 3 * pix); vg = __ldg(v_out + 3 * pix + 1); vb = __ldg(v_out + 3 * pix + 2);
-            if (v_scale) {                  // upstream gradient of a scalar loss whose d/d out_img is already in v_out
-                const float sc = __ldg(v_scale);
-                vr *= sc; vg *= sc; vb *= sc;
+    int q = first;
+    int2 c_nx = q < n_items ? pipe.load_range(q) : make_int2(0, 0);
+    for (; q < n_items; q += stride) {
+        const int2 rg = c_nx;
+        if (q + stride < n_items) c_nx = pipe.load_range(q + stride);
+        const int lo = rg.x, cnt = rg.y;
+        if (cnt <= pipe.c_first) continue;                 // nothing for this item in the tile
+        const int k = q >> ishift;
+        const int ty = k / TX, tx = k - ty * TX;
+        const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
+        // the tile of upstream gradients, zero outside the image (such pixels then contribute exact zeros)
+        if (vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H) {
+#pragma unroll
+            for (int q = 0; q < 6; ++q) {                   // 16 rows x 12 float4
+                const int f = q * 32 + lane, row = f / 12, c4 = f - row * 12;
+                const float4 g4 = __ldg(reinterpret_cast<const float4 *>(v_out + ((size_t)(ty0 + row) * W + tx0) * 3) + c4);
+                const float e[4] = {g4.x, g4.y, g4.z, g4.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int fl = 4 * c4 + j, px = fl / 3, ch = fl - 3 * px;
+                    S.v[ch][row * GI2D_TILE + px] = e[j] * vsc;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int p = q * 32 + lane, j = tx0 + (p & 15), i = ty0 + (p >> 4);
+                float vr = 0.f, vg = 0.f, vb = 0.f;
+                if (i < H && j < W) {
+                    const size_t pix = (size_t)i * W + j;
+                    vr = __ldg(v_out + 3 * pix) * vsc; vg = __ldg(v_out + 3 * pix + 1) * vsc; vb = __ldg(v_out + 3 * pix + 2) * vsc;
+                }
+                S.v[0][p] = vr; S.v[1][p] = vg; S.v[2][p] = vb;
             }
         }
-        s_v[0][tid] = vr; s_v[1][tid] = vg; s_v[2][tid] = vb;
-    }
-    stage_records<TMA>(s_rec, &s_bar, packed, src, lo, cnt);
+        // (visibility of S.v to the other lanes: the __syncwarp after the prefix stores below)
 
-    // per record: visible rectangle -> rows x aligned 4-pixel groups = units; block-wide exclusive scan of the unit counts
-    int units = 0;
-    {
-        int lx0 = 0, lx1 = 0, ly0 = 0, ly1 = 0;
-        uint32_t rect = 0;
-        if (tid < cnt && record_rect(s_rec[3 * tid], s_rec[3 * tid + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
-            const int g0 = lx0 >> 2, segs = (lx1 >> 2) - g0 + 1, rows = ly1 - ly0 + 1;
-            units = rows * segs;
-            rect = (uint32_t)lx0 | ((uint32_t)lx1 << 4) | ((uint32_t)ly0 << 8) | ((uint32_t)g0 << 12) | ((uint32_t)segs << 14) |
-                   ((uint32_t)rows << 17);
-        }
-        s_rect[tid] = rect;
-    }
-    int incl = units;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += t;
-    }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    int wbase = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < RB / 32; ++w) {
-        const int c = s_warp[w];
-        wbase += (w < warp) ? c : 0;
-        total += c;
-    }
-    s_pref[tid] = (uint16_t)(wbase + incl - units);
-    if (tid == 0) s_pref[RB] = (uint16_t)total;
-    __syncthreads();
-    if (total == 0) return;
-
-    // ---- main loop: this thread's contiguous chunk of the flattened unit list
-    const int R = (total + RB - 1) / RB;
-    int u = tid * R;
-    const int uend = min(total, u + R);
-    if (u < uend) {
-        // record containing unit u: the largest t with s_pref[t] <= u (records without units share their successor's prefix)
-        int t = 0;
-#pragma unroll
-        for (int step = RB / 2; step > 0; step >>= 1)
-            if ((int)s_pref[t + step] <= u) t += step;
-        float S_m = 0.f, S_x = 0.f, S_y = 0.f, S_xx = 0.f, S_xy = 0.f, S_yy = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f;
-        // current record (registers) and position (row, seg) inside its rectangle
-        float x, y, opac, cx, cy, cz, cr, cg, cb;
-        int x0, x1, y0, g0, segs, rec_end, row, seg;
-        auto load_record = [&]() {
-            const float4 A = s_rec[3 * t], B = s_rec[3 * t + 1];
-            cb = s_rec[3 * t + 2].x;
-            x = A.x; y = A.y; opac = A.z; cx = A.w; cy = B.x; cz = B.y; cr = B.z; cg = B.w;
-            const uint32_t rect = s_rect[t];
-            x0 = rect & 15; x1 = (rect >> 4) & 15; y0 = (rect >> 8) & 15; g0 = (rect >> 12) & 3; segs = (rect >> 14) & 7;
-            rec_end = (int)s_pref[t + 1];
-            const int k = u - (int)s_pref[t];
-            row = segs == 1 ? k : segs == 2 ? (k >> 1) : segs == 4 ? (k >> 2) : ((k * 43) >> 7);
-            seg = k - row * segs;
-        };
-        auto flush = [&]() {
-            const int slot = tid + t;
-            s_part[0][slot] = S_x; s_part[1][slot] = S_y; s_part[2][slot] = S_xx; s_part[3][slot] = S_xy; s_part[4][slot] = S_yy;
-            s_part[5][slot] = a_r; s_part[6][slot] = a_g; s_part[7][slot] = a_b; s_part[8][slot] = S_m;
-        };
-        load_record();
-        // ONE flat loop over the chunk: crossing into the next record is a short divergent branch, the four-pixel body
-        // stays converged across the warp (an inner per-record loop would make lanes wait for each other's records)
-        for (; u < uend; ++u) {
-            if (u >= rec_end) {
-                flush();
-                S_m = S_x = S_y = S_xx = S_xy = S_yy = a_r = a_g = a_b = 0.f;
-                do { ++t; } while ((int)s_pref[t + 1] <= u);        // next record that has units
-                load_record();
+        for (int off = pipe.c_first; off < cnt; off += pipe.c_step) {
+            const int n = min(PIPE_CHUNK, cnt - off);
+            float4 *rec;
+            if (TMA) {
+                rec = pipe.acquire();
+            } else {
+                rec = pipe.ring;
+                gather_chunk(rec, src, lo + off, n, lane);
             }
-            const int ly = y0 + row, g = g0 + seg;
-            const float dy = fsub(y, (float)(ty0 + ly));
-            const float t3 = fmul(dy, fmul(cz, dy));
-            const float4 vr4 = reinterpret_cast<const float4 *>(s_v[0])[ly * 4 + g];
-            const float4 vg4 = reinterpret_cast<const float4 *>(s_v[1])[ly * 4 + g];
-            const float4 vb4 = reinterpret_cast<const float4 *>(s_v[2])[ly * 4 + g];
-            const float vr[4] = {vr4.x, vr4.y, vr4.z, vr4.w}, vg[4] = {vg4.x, vg4.y, vg4.z, vg4.w}, vb[4] = {vb4.x, vb4.y, vb4.z, vb4.w};
-            const float fx0 = (float)(tx0 + 4 * g);
-            float u_m = 0.f, u_x = 0.f;              // this unit's sum m and sum m dx (dy is constant over the unit)
+            // per record: visible rectangle -> the aligned 4x2 pixel blocks it touches = units; warp-wide exclusive scan of the counts
+            int units[2], ubeg[2];
+            int run = 0;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int lx = 4 * g + j;
-                const float dx = fsub(x, fx0 + (float)j);
-                const float q = ffma(dx, fmul(cx, dx), t3);
-                const float sigma = ffma(dy, fmul(cy, dx), fmul(q, 0.5f));
-                const float vis = exp_neg(sigma);
-                const float raw = fminf(fmul(opac, vis), 1.f);
-                const bool valid = lx >= x0 && lx <= x1 && !(sigma < 0.f) && !(raw < GI2D_ALPHA_MIN);   // backward.cu:806-808
-                const float alpha = valid ? raw : 0.f;
-                a_r = fmaf(alpha, vr[j], a_r); a_g = fmaf(alpha, vg[j], a_g); a_b = fmaf(alpha, vb[j], a_b);   // backward.cu:814
-                const float v_alpha = fmaf(cr, vr[j], fmaf(cg, vg[j], cb * vb[j]));                          // :818-820
-                const float m = valid ? vis * v_alpha : 0.f;
-                const float mdx = m * dx;
-                u_m += m;
-                u_x += mdx;
-                S_xx = fmaf(mdx, dx, S_xx);
+            for (int h = 0; h < 2; ++h) {
+                const int t = 32 * h + lane;
+                int lx0 = 0, lx1 = 0, ly0 = 0, ly1 = 0, un = 0;
+                uint32_t rect = 0;
+                if (t < n && record_rect(rec[3 * t], rec[3 * t + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
+                    const int bx0 = lx0 >> 2, nbx = (lx1 >> 2) - bx0 + 1, by0 = ly0 >> 1, nby = (ly1 >> 1) - by0 + 1;
+                    un = nbx * nby;
+                    rect = (uint32_t)bx0 | ((uint32_t)nbx << 2) | ((uint32_t)by0 << 5);
+                }
+                S.rect[t] = (uint8_t)rect;
+                int incl = un;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                units[h] = un;
+                ubeg[h] = run + incl - un;
+                S.pref[t] = (uint16_t)ubeg[h];
+                run += __shfl_sync(0xffffffffu, incl, 31);
             }
-            S_m += u_m; S_x += u_x;
-            const float mdy = u_m * dy;
-            S_y += mdy;
-            S_yy = fmaf(mdy, dy, S_yy);
-            S_xy = fmaf(u_x, dy, S_xy);
-            if (++seg == segs) { seg = 0; ++row; }
+            const int total = run;
+            if (lane == 0) S.pref[PIPE_CHUNK] = (uint16_t)total;
+            __syncwarp();
+            if (total > 0) {
+                // ---- main loop: this lane's contiguous piece of the flattened unit list
+                const int R = (total + 31) >> 5;
+                int u = lane * R;
+                const int uend = min(total, u + R);
+                if (u < uend) {
+                    // record containing unit u: the largest t with pref[t] <= u (records without units share their successor's prefix)
+                    int t = 0;
+#pragma unroll
+                    for (int step = PIPE_CHUNK / 2; step > 0; step >>= 1)
+                        if ((int)S.pref[t + step] <= u) t += step;
+                    float S_m = 0.f, S_x = 0.f, S_y = 0.f, S_xx = 0.f, S_xy = 0.f, S_yy = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f;
+                    // current record (registers) and its block range
+                    float x, y, opac, cx, cy, cz, cr, cg, cb;
+                    int bx0, nbx, by0, base, rec_end;
+                    size_t gid;
+                    auto load_record = [&]() {
+                        const float4 A = rec[3 * t], B = rec[3 * t + 1];
+                        const float2 C = *reinterpret_cast<const float2 *>(&rec[3 * t + 2]);
+                        cb = C.x; gid = (size_t)__float_as_int(C.y);
+                        x = A.x; y = A.y; opac = A.z; cx = A.w; cy = B.x; cz = B.y; cr = B.z; cg = B.w;
+                        const uint32_t rect = S.rect[t];
+                        bx0 = rect & 3; nbx = (rect >> 2) & 7; by0 = rect >> 5;
+                        base = (int)S.pref[t];
+                        rec_end = (int)S.pref[t + 1];
+                    };
+                    // this lane's share of the record's gradients -> ONE set of global reductions (linear in the sums, so
+                    // the shares of the lanes that split a record simply add up in memory like those of other tiles do)
+                    auto flush = [&]() {
+                        if (S_x == 0.f && S_y == 0.f && S_xx == 0.f && S_xy == 0.f && S_yy == 0.f && a_r == 0.f && a_g == 0.f && a_b == 0.f && S_m == 0.f)
+                            return;
+                        const float nop = -opac, hop = -0.5f * opac;              // v_sigma = -opac * m ; the conic terms carry 0.5 (Q7)
+                        const float g_x = nop * fmaf(cx, S_x, cy * S_y), g_y = nop * fmaf(cy, S_x, cz * S_y);   // backward.cu:826-827
+                        const float g_cxx = hop * S_xx, g_cxy = hop * S_xy, g_cyy = hop * S_yy;                // :823-825
+                        if (VEC12) {
+                            float *row = out.g12 + 12 * gid;
+                            red_add_v4(row, g_x, g_y, g_cxx, g_cxy);
+                            red_add_v4(row + 4, g_cyy, a_r, a_g, a_b);
+                            atomicAdd(row + 8, S_m);
+                        } else {
+                            atomicAdd(out.v_xy + 2 * gid, g_x); atomicAdd(out.v_xy + 2 * gid + 1, g_y);
+                            atomicAdd(out.v_conic + 3 * gid, g_cxx); atomicAdd(out.v_conic + 3 * gid + 1, g_cxy); atomicAdd(out.v_conic + 3 * gid + 2, g_cyy);
+                            atomicAdd(out.v_colors + 3 * gid, a_r); atomicAdd(out.v_colors + 3 * gid + 1, a_g); atomicAdd(out.v_colors + 3 * gid + 2, a_b);
+                            atomicAdd(out.v_opacity + gid, S_m);
+                        }
+                    };
+                    load_record();
+                    // ONE flat loop over the piece: crossing into the next record is a short divergent branch (flush, find, load),
+                    // the eight-pixel body stays converged across the warp
+                    for (; u < uend; ++u) {
+                        if (u >= rec_end) {
+                            flush();
+                            S_m = S_x = S_y = S_xx = S_xy = S_yy = a_r = a_g = a_b = 0.f;
+                            do { ++t; } while ((int)S.pref[t + 1] <= u);        // next record that has units
+                            load_record();
+                        }
+                        const int kk = u - base;
+                        const int rowb = nbx == 1 ? kk : nbx == 2 ? (kk >> 1) : nbx == 4 ? (kk >> 2) : ((kk * 43) >> 7);
+                        const int bx = bx0 + kk - rowb * nbx, ly0 = 2 * (by0 + rowb);
+                        const float fx0 = (float)(tx0 + 4 * bx);
+                        float dx[4], cu[4], cw[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            dx[j] = fsub(x, fx0 + (float)j);
+                            cu[j] = fmul(cx, dx[j]);
+                            cw[j] = fmul(cy, dx[j]);
+                        }
+                        // Pixels of the block outside the record's rectangle need no test of their own: the rectangle is a
+                        // conservative bound of where the alpha test can pass, so that test rejects them (as in the forward).
+#pragma unroll
+                        for (int r = 0; r < 2; ++r) {
+                            const int ly = ly0 + r;
+                            const float dy = fsub(y, (float)(ty0 + ly));
+                            const float t3 = fmul(dy, fmul(cz, dy));
+                            const float4 vr4 = reinterpret_cast<const float4 *>(S.v[0])[ly * 4 + bx];
+                            const float4 vg4 = reinterpret_cast<const float4 *>(S.v[1])[ly * 4 + bx];
+                            const float4 vb4 = reinterpret_cast<const float4 *>(S.v[2])[ly * 4 + bx];
+                            const float vr[4] = {vr4.x, vr4.y, vr4.z, vr4.w}, vg[4] = {vg4.x, vg4.y, vg4.z, vg4.w}, vb[4] = {vb4.x, vb4.y, vb4.z, vb4.w};
+                            float u_m = 0.f, u_x = 0.f;          // this row's sum m and sum m dx (dy is constant over the row)
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const float q = ffma(dx[j], cu[j], t3);
+                                const float sigma = ffma(dy, cw[j], fmul(q, 0.5f));
+                                const float vis = exp_neg(sigma);
+                                const float raw = fminf(fmul(opac, vis), 1.f);
+                                const bool valid = !(sigma < 0.f) && !(raw < GI2D_ALPHA_MIN);                               // backward.cu:806-808
+                                const float alpha = valid ? raw : 0.f;
+                                a_r = fmaf(alpha, vr[j], a_r); a_g = fmaf(alpha, vg[j], a_g); a_b = fmaf(alpha, vb[j], a_b);   // backward.cu:814
+                                const float v_alpha = fmaf(cr, vr[j], fmaf(cg, vg[j], cb * vb[j]));                          // :818-820
+                                const float m = valid ? vis * v_alpha : 0.f;
+                                const float mdx = m * dx[j];
+                                u_m += m;
+                                u_x += mdx;
+                                S_xx = fmaf(mdx, dx[j], S_xx);
+                            }
+                            S_m += u_m; S_x += u_x;
+                            const float mdy = u_m * dy;
+                            S_y += mdy;
+                            S_yy = fmaf(mdy, dy, S_yy);
+                            S_xy = fmaf(u_x, dy, S_xy);
+                        }
+                    }
+                    flush();
+                }
+            }
+            __syncwarp();                                  // every lane has left the stage, rect / pref are free again
+            if (TMA) pipe.release();
         }
-        flush();
-    }
-    __syncthreads();
-    if (tid >= cnt || units == 0) return;
-    float S_x = 0.f, S_y = 0.f, S_xx = 0.f, S_xy = 0.f, S_yy = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f, S_m = 0.f;
-    {
-        const int ubeg = (int)s_pref[tid];
-        const int ta = ubeg / R, tb = (ubeg + units - 1) / R;           // threads whose chunks intersect this record
-        for (int slot = ta + tid; slot <= tb + tid; ++slot) {
-            S_x += s_part[0][slot]; S_y += s_part[1][slot]; S_xx += s_part[2][slot]; S_xy += s_part[3][slot]; S_yy += s_part[4][slot];
-            a_r += s_part[5][slot]; a_g += s_part[6][slot]; a_b += s_part[7][slot]; S_m += s_part[8][slot];
-        }
-    }
-    if (S_x == 0.f && S_y == 0.f && S_xx == 0.f && S_xy == 0.f && S_yy == 0.f && a_r == 0.f && a_g == 0.f && a_b == 0.f && S_m == 0.f)
-        return;
-    const float4 A = s_rec[3 * tid], B = s_rec[3 * tid + 1];
-    const float nop = -A.z, hop = -0.5f * A.z;                 // v_sigma = -opac * m ; the conic terms carry 0.5 (Q7)
-    const float g_x = nop * fmaf(A.w, S_x, B.x * S_y), g_y = nop * fmaf(B.x, S_x, B.y * S_y);   // backward.cu:826-827
-    const float g_cxx = hop * S_xx, g_cxy = hop * S_xy, g_cyy = hop * S_yy;                    // :823-825
-    const size_t gid = (size_t)__float_as_int(s_rec[3 * tid + 2].y);
-    if (VEC12) {
-        float *row = out.g12 + 12 * gid;
-        red_add_v4(row, g_x, g_y, g_cxx, g_cxy);
-        red_add_v4(row + 4, g_cyy, a_r, a_g, a_b);
-        atomicAdd(row + 8, S_m);
-    } else {
-        atomicAdd(out.v_xy + 2 * gid, g_x); atomicAdd(out.v_xy + 2 * gid + 1, g_y);
-        atomicAdd(out.v_conic + 3 * gid, g_cxx); atomicAdd(out.v_conic + 3 * gid + 1, g_cxy); atomicAdd(out.v_conic + 3 * gid + 2, g_cyy);
-        atomicAdd(out.v_colors + 3 * gid, a_r); atomicAdd(out.v_colors + 3 * gid + 1, a_g); atomicAdd(out.v_colors + 3 * gid + 2, a_b);
-        atomicAdd(out.v_opacity + gid, S_m);
     }
 }
 
@@ -528,43 +681,85 @@ static inline int cuda_status() {
 // float4 image stores need 16-byte aligned rows: W % 4 == 0 and an aligned base (nullptr counts as aligned).
 static inline int vec_ok(int W, const void *base) { return (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0); }
 
-// The rasterizers are limited to 4 CTAs/SM by registers; ask for the shared-memory carve-out that lets 4 of them fit.
+// Persistent grids: as many CTAs as are co-resident (SMs x occupancy), never more than there are tiles (tiles are dealt to
+// CTAs first, then to the warps of a CTA, so a grid larger than tiles / 8 only leaves warp slots empty).
 template <typename K>
-static void prefer_shared(K kernel) {
-    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-}
-// Persistent forward grid: as many CTAs as are co-resident (SMs x occupancy), never more than there are tiles.
-template <typename K>
-static int fwd_grid(K kernel, int n_tiles) {
+static int persistent_grid(K kernel, int threads, size_t smem, int n_tiles, const char *env_cap) {
     static int sms = 0;
     if (!sms) {
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
-    static const void *keys[8];
-    static int vals[8], used = 0;
+    static const void *keys[16];
+    static int vals[16], used = 0;
     const void *key = reinterpret_cast<const void *>(kernel);
     int per_sm = 0;
     for (int i = 0; i < used; ++i)
         if (keys[i] == key) per_sm = vals[i];
     if (!per_sm) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RB, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
-        if (used < 8) { keys[used] = key; vals[used] = per_sm; ++used; }
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+        const char *v = getenv(env_cap);                  // experiments: GI2D_FWD_CTAS_PER_SM / GI2D_BWD_CTAS_PER_SM
+        if (v && atoi(v) > 0 && per_sm > atoi(v)) per_sm = atoi(v);
+        if (used < 16) { keys[used] = key; vals[used] = per_sm; ++used; }
         cudaGetLastError();
     }
     const int g = sms * per_sm;
-    return n_tiles < g ? n_tiles : g;
+    return n_tiles < g ? (n_tiles < 1 ? 1 : n_tiles) : g;
 }
-
-static void init_once() {
-    static bool done = false;
-    if (done) return;
-    done = true;
-    prefer_shared(raster_bwd_kernel<true, true>);
-    prefer_shared(raster_bwd_kernel<false, false>);
-    cudaGetLastError();
+template <typename K>
+static int fwd_grid(K kernel, int n_items) { return persistent_grid(kernel, FW_THREADS, FW_SMEM, n_items, "GI2D_FWD_CTAS_PER_SM"); }
+// Warps per tile of the forward rasterizer.  One: two half-tile warps double the warps in flight but rebuild the masks twice
+// (+21 % instructions) and were not faster on any configuration (B200, CUPTI: 768x512 / 70k 15.3 vs 15.9 us, 1020x678 / 100k
+// 19.8 vs 21.8 us, 8K / 1M 206 vs 276 us); GI2D_FWD_SPLIT=2 keeps the variant reachable for experiments.
+static int fwd_split(int n_tiles) {
+    static const int forced = getenv("GI2D_FWD_SPLIT") ? atoi(getenv("GI2D_FWD_SPLIT")) : 0;
+    (void)n_tiles;
+    return forced == 2 ? 2 : 1;
+}
+struct FwdArgs {
+    int TX, W, H, tile_begin, n_tiles;
+    int *tile_bins;
+    const float4 *packed;
+    GatherSrc src;
+    const int *d_status;
+    const float *background;
+    float *out_img, *final_Ts;
+    int *final_idx;
+    float *out_mc;
+    int vec_ok;
+    LossArgs la;
+};
+template <bool TMA, bool AUX, bool LOSS>
+static int fwd_grid_for(int n_tiles) {
+    return fwd_split(n_tiles) == 2 ? fwd_grid(raster_fwd_kernel<TMA, AUX, LOSS, 2>, 2 * n_tiles) : fwd_grid(raster_fwd_kernel<TMA, AUX, LOSS, 1>, n_tiles);
+}
+template <bool TMA, bool AUX, bool LOSS>
+static void launch_fwd(const FwdArgs &a, cudaStream_t stream) {
+    const int grid = fwd_grid_for<TMA, AUX, LOSS>(a.n_tiles);
+    if (fwd_split(a.n_tiles) == 2)
+        raster_fwd_kernel<TMA, AUX, LOSS, 2><<<grid, FW_THREADS, FW_SMEM, stream>>>(a.TX, a.W, a.H, a.tile_begin, a.n_tiles, a.tile_bins, a.packed, a.src, a.d_status,
+                                                                                   a.background, a.out_img, a.final_Ts, a.final_idx, a.out_mc, a.vec_ok, a.la);
+    else
+        raster_fwd_kernel<TMA, AUX, LOSS, 1><<<grid, FW_THREADS, FW_SMEM, stream>>>(a.TX, a.W, a.H, a.tile_begin, a.n_tiles, a.tile_bins, a.packed, a.src, a.d_status,
+                                                                                   a.background, a.out_img, a.final_Ts, a.final_idx, a.out_mc, a.vec_ok, a.la);
+}
+template <typename K>
+static int bwd_grid(K kernel, int n_items) { return persistent_grid(kernel, BW_THREADS, BW_SMEM, n_items, "GI2D_BWD_CTAS_PER_SM"); }
+// log2 of the warps per tile of the backward rasterizer (they split the tile's chunks of 64 records): 2 warps per tile when
+// the image has so few tiles that one warp per tile leaves most warp slots of the 148 SMs empty AND a tile has more than
+// one chunk to split (the projections of this path give ~2.5 intersections per Gaussian).  Measured on B200
+// (CUPTI kernel time, L2 flushed): 768x512 / 70k (1536 tiles) 23.5 -> 21.1 us; 1020x678 / 100k (2752 tiles) 29.3 -> 32.4 us;
+// 768x512 / 10k 9.2 -> 11.8 us; four warps per tile are slower everywhere.
+static int bwd_ishift(int N, int n_tiles) {
+    static const int forced = getenv("GI2D_BWD_SPLIT") ? atoi(getenv("GI2D_BWD_SPLIT")) : 0;
+    if (forced == 1) return 0;
+    if (forced == 2) return 1;
+    if (forced == 4) return 2;
+    const double per_tile = 2.5 * (double)N / (double)n_tiles;
+    return (n_tiles <= 2048 && per_tile > 64.0) ? 1 : 0;
 }
 
 }  // namespace gi2d
@@ -580,10 +775,10 @@ int gi2d_raster_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, co
                         float *final_Ts, int *final_idx, cudaStream_t stream) {
     if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0) return GI2D_ERR_INVALID;
     GatherSrc src{gids_sorted, xys, conics, colors, opacities};
-    if (final_Ts && final_idx)
-        raster_fwd_kernel<false, true><<<fwd_grid(raster_fwd_kernel<false, true>, TX * TY), RB, 0, stream>>>(TX, W, H, 0, TX * TY, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx, nullptr, vec_ok(W, out_img));
-    else
-        raster_fwd_kernel<false, false><<<fwd_grid(raster_fwd_kernel<false, false>, TX * TY), RB, 0, stream>>>(TX, W, H, 0, TX * TY, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, nullptr, nullptr, nullptr, vec_ok(W, out_img));
+    const FwdArgs a{TX, W, H, 0, TX * TY, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx, nullptr,
+                    vec_ok(W, out_img), LossArgs{}};
+    if (final_Ts && final_idx) launch_fwd<false, true, false>(a, stream);
+    else launch_fwd<false, false, false>(a, stream);
     return cuda_status();
 }
 
@@ -597,10 +792,9 @@ int gi2d_raster_sum_fwd_packed_rows_mc(int TX, int TY, int W, int H, int ty_begi
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     const float4 *p = reinterpret_cast<const float4 *>(packed);
     const int nt = (ty_end - ty_begin) * TX, first = ty_begin * TX;
-    if (final_Ts && final_idx)
-        raster_fwd_kernel<true, true><<<fwd_grid(raster_fwd_kernel<true, true>, nt), RB, 0, stream>>>(TX, W, H, first, nt, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx, out_img_mc, vok);
-    else
-        raster_fwd_kernel<true, false><<<fwd_grid(raster_fwd_kernel<true, false>, nt), RB, 0, stream>>>(TX, W, H, first, nt, tile_bins, p, src, d_status, background, out_img, nullptr, nullptr, out_img_mc, vok);
+    const FwdArgs a{TX, W, H, first, nt, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx, out_img_mc, vok, LossArgs{}};
+    if (final_Ts && final_idx) launch_fwd<true, true, false>(a, stream);
+    else launch_fwd<true, false, false>(a, stream);
     return cuda_status();
 }
 
@@ -626,14 +820,14 @@ int gi2d_raster_sum_bwd(int N, int TX, int TY, int W, int H, const int *gids_sor
                         float *v_opacity, cudaStream_t stream) {
     (void)final_idx;
     if (N <= 0 || TX <= 0 || TY <= 0) return GI2D_ERR_INVALID;
-    init_once();
     cudaMemsetAsync(v_xy, 0, sizeof(float) * 2 * (size_t)N, stream);
     cudaMemsetAsync(v_conic, 0, sizeof(float) * 3 * (size_t)N, stream);
     cudaMemsetAsync(v_colors, 0, sizeof(float) * 3 * (size_t)N, stream);
     cudaMemsetAsync(v_opacity, 0, sizeof(float) * (size_t)N, stream);
     GatherSrc src{gids_sorted, xys, conics, colors, opacities};
     GradOut out{nullptr, v_xy, v_conic, v_colors, v_opacity};
-    raster_bwd_kernel<false, false><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, nullptr, src, v_out, out);
+    const int ish = bwd_ishift(N, TX * TY);
+    raster_bwd_kernel<false, false><<<bwd_grid(raster_bwd_kernel<false, false>, (TX * TY) << ish), BW_THREADS, BW_SMEM, stream>>>(TX, W, H, TX * TY, ish, tile_bins, nullptr, src, v_out, out, vec_ok(W, v_out));
     return cuda_status();
 }
 
@@ -644,11 +838,11 @@ int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *t
                                const float *v_out, float *grads12, cudaStream_t stream) {
     if (N <= 0 || TX <= 0 || TY <= 0) return GI2D_ERR_INVALID;
     if (reinterpret_cast<uintptr_t>(grads12) & 15) return GI2D_ERR_INVALID;
-    init_once();
     cudaMemsetAsync(grads12, 0, sizeof(float) * 12 * (size_t)N, stream);
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     GradOut out{grads12, nullptr, nullptr, nullptr, nullptr};
-    raster_bwd_kernel<true, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out, out);
+    const int ish = bwd_ishift(N, TX * TY);
+    raster_bwd_kernel<true, true><<<bwd_grid(raster_bwd_kernel<true, true>, (TX * TY) << ish), BW_THREADS, BW_SMEM, stream>>>(TX, W, H, TX * TY, ish, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out, out, vec_ok(W, v_out));
     return cuda_status();
 }
 
@@ -660,21 +854,22 @@ int gi2d_raster_sum_fwd_packed_mse(int TX, int TY, int W, int H, int *tile_bins,
                                    float *image, float *loss, void *ws, size_t ws_bytes, cudaStream_t stream) {
     if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0 || !gt || !v_out || !loss || !ws) return GI2D_ERR_INVALID;
     const int nt = TX * TY;
-    const int grid = fwd_grid(raster_fwd_kernel<true, false, true>, nt);
+    const int grid = fwd_grid_for<true, false, true>(nt);
     if (ws_bytes < sizeof(float) * (size_t)grid + 16) return GI2D_ERR_WORKSPACE;
     LossArgs la{gt, gt_is_chw ? 1 : 0, clamp01 ? 1 : 0, 1.f / (3.f * (float)H * (float)W), v_out, image,
                 reinterpret_cast<float *>(reinterpret_cast<char *>(ws) + 16), reinterpret_cast<unsigned int *>(ws), loss};
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
-    raster_fwd_kernel<true, false, true><<<grid, RB, 0, stream>>>(TX, W, H, 0, nt, tile_bins, reinterpret_cast<const float4 *>(packed), src,
-                                                                 d_status, background, nullptr, nullptr, nullptr, nullptr,
-                                                                 vec_ok(W, v_out), la);
+    const FwdArgs a{TX, W, H, 0, nt, tile_bins, reinterpret_cast<const float4 *>(packed), src, d_status, background, nullptr, nullptr, nullptr,
+                    nullptr, vec_ok(W, v_out), la};
+    launch_fwd<true, false, true>(a, stream);
     return cuda_status();
 }
 
 // Workspace of gi2d_raster_sum_fwd_packed_mse: a ticket word (must be ZERO before the first call; the kernel leaves it
 // zero) and one partial sum per resident CTA.
 size_t gi2d_raster_mse_workspace_bytes(void) {
-    return 16 + sizeof(float) * (size_t)fwd_grid(raster_fwd_kernel<true, false, true>, 1 << 30);
+    const int g1 = fwd_grid(raster_fwd_kernel<true, false, true, 1>, 1 << 30), g2 = fwd_grid(raster_fwd_kernel<true, false, true, 2>, 1 << 30);
+    return 16 + sizeof(float) * (size_t)(g1 > g2 ? g1 : g2);
 }
 
 // gi2d_raster_sum_bwd_packed with v_out multiplied by the device scalar *v_scale (the upstream gradient of the loss).
@@ -682,11 +877,11 @@ int gi2d_raster_sum_bwd_packed_scaled(int N, int TX, int TY, int W, int H, const
                                       const float *v_out, const float *v_scale, float *grads12, cudaStream_t stream) {
     if (N <= 0 || TX <= 0 || TY <= 0) return GI2D_ERR_INVALID;
     if (reinterpret_cast<uintptr_t>(grads12) & 15) return GI2D_ERR_INVALID;
-    init_once();
     cudaMemsetAsync(grads12, 0, sizeof(float) * 12 * (size_t)N, stream);
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     GradOut out{grads12, nullptr, nullptr, nullptr, nullptr};
-    raster_bwd_kernel<true, true><<<TX * TY, RB, 0, stream>>>(TX, W, H, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out, out, v_scale);
+    const int ish = bwd_ishift(N, TX * TY);
+    raster_bwd_kernel<true, true><<<bwd_grid(raster_bwd_kernel<true, true>, (TX * TY) << ish), BW_THREADS, BW_SMEM, stream>>>(TX, W, H, TX * TY, ish, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out, out, vec_ok(W, v_out), v_scale);
     return cuda_status();
 }
 

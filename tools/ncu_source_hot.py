@@ -1,12 +1,15 @@
 """Hot spots of one kernel from an ncu report captured with --import-source on: segments between barriers / mbarrier waits
 with their share of the stall samples and of the executed instructions, and every instruction above 1.5 % of the samples.
-python tools/ncu_source_hot.py gpurun_out/r01_fwd_c5.ncu-rep"""
+python tools/ncu_source_hot.py gpurun_out/r01_fwd_c5.ncu-rep [kernel-name-regex]"""
 import csv
 import io
 import subprocess
 import sys
 
-raw = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "source", "--csv"], capture_output=True, text=True).stdout
+cmd = ["ncu", "-i", sys.argv[1], "--page", "source", "--csv"]
+if len(sys.argv) > 2:          # a report with several kernels: pick one by (regex) name; the first matching launch is shown
+    cmd += ["--kernel-name", "regex:" + sys.argv[2], "--launch-count", "1"] if False else ["--kernel-name", "regex:" + sys.argv[2]]
+raw = subprocess.run(cmd, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr = rows[1]
 idx = {h: i for i, h in enumerate(hdr)}
