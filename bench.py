@@ -274,7 +274,7 @@ def kernel_rooflines(step, flush, reps, peaks, sm_mhz):
     import torch
     from gaussianimage_b200 import cuda as GC
     from gaussianimage_b200._lib import check, lib
-    from gaussianimage_b200.rasterize_sum import _capacity, fused_chain
+    from gaussianimage_b200.rasterize_sum import fused_chain, get_capacity
     import gaussianimage_b200 as G
     s = step.s
     H, W, (TX, TY, _) = s.H, s.W, s.tile_bounds
@@ -287,7 +287,7 @@ def kernel_rooflines(step, flush, reps, peaks, sm_mhz):
             if step.param == "rs" else (lambda: GC.project_gaussians_2d_forward(means.shape[0], means, p[0], H, W, s.tile_bounds))
         xys, depths, radii, conics, nth = proj()
         N = xys.shape[0]
-        cap = _capacity[(dev.index, N, TX, TY)]
+        cap = get_capacity(dev.index, N, TX, TY) or max(4 * N, 1 << 14)
         r = fused_chain(xys, radii, conics, nth, colors, opac, step.bg, H, W, cap)
         n_isect = int(r["status"][0].item())
         E = count_evals(r["tile_bins"], H, W)

@@ -26,6 +26,7 @@ _SIGNATURES = {
     "gi2d_project_scale_rot_bwd": (_i, [_i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_project_cholesky_bwd_packed": (_i, [_i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_project_scale_rot_bwd_packed": (_i, [_i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gi2d_project_fwd_total": (_i, [_i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_cov2d_bounds": (_i, [_i, _vp, _vp, _vp, _vp]),
     "gi2d_scan_workspace_bytes": (_sz, [_i]),
     "gi2d_scan_tiles": (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp]),
@@ -43,6 +44,9 @@ _SIGNATURES = {
     "gi2d_raster_sum_fwd_packed_mse": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gi2d_raster_sum_bwd_packed_scaled": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_repack_records": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gi2d_repack_records_ex": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "gi2d_bin_fused_ex": (_i, [_vp, _vp]),
+    "gi2d_raster_sum_bwd_packed_acc": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_bin_fused": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_bin_fused_rows": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_bin_fused_rows_notify": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp]),
@@ -54,6 +58,14 @@ _SIGNATURES = {
     "gi2d_raster_sum_bwd_packed": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
 }
 EXPORTS = tuple(_SIGNATURES)
+
+
+class BinArgs(C.Structure):
+    """struct gi2d_bin_args of include/gi2d.h."""
+    _fields_ = [("N", _i), ("TX", _i), ("TY", _i), ("ty_begin", _i), ("ty_end", _i), ("capacity", _i),
+                ("xys", _vp), ("radii", _vp), ("num_tiles_hit", _vp), ("conics", _vp), ("colors", _vp), ("opacities", _vp),
+                ("ws", _vp), ("ws_bytes", _sz), ("gids_sorted", _vp), ("tile_bins", _vp), ("packed", _vp),
+                ("status_out", _vp), ("status_host", _vp), ("status_sticky", _vp), ("zero_grads12", _vp)]
 
 
 def build(verbose: bool = False) -> Path:
@@ -118,18 +130,19 @@ def glue():
                 warnings.warn(f"gi2d: host glue {GLUE_PATH.name} could not be loaded ({e}); using the ctypes host path "
                               "(same kernels). Rebuild with `python -c 'import __graft_entry__ as g; g.build()'`.")
                 return None
-            if mod.abi_version() != 1:
+            if mod.abi_version() != 2:
                 raise RuntimeError("_gi2d_torch.so was built against another libgi2d ABI")
             _glue = mod
     return _glue
 
 
-_cpp_autograd = os.environ.get("GI2D_CPP_AUTOGRAD", "0") == "1"
+_cpp_autograd = os.environ.get("GI2D_CPP_AUTOGRAD", "1") != "0"
 
 
 def cpp_autograd():
-    """The glue module when the operators should run as C++ autograd Functions (csrc/torch_glue.cpp: ProjectFn,
-    RasterFusedFn) instead of Python ones -- opt-in, GI2D_CPP_AUTOGRAD=1 or set_cpp_autograd(True) -- else None."""
+    """The glue module when the operators run as C++ autograd Functions with the fused chain's policy in C++
+    (csrc/torch_glue.cpp: ProjectFn, RasterFn, rasterize) -- the default whenever the glue is built -- else None:
+    GI2D_CPP_AUTOGRAD=0 / set_cpp_autograd(False) select the Python autograd Functions over the same kernels."""
     return glue() if _cpp_autograd else None
 
 
@@ -150,7 +163,7 @@ def lib() -> C.CDLL:
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(L, name)      # AttributeError here = header/library mismatch
             fn.restype, fn.argtypes = res, args
-        if L.gi2d_abi_version() != 1:
+        if L.gi2d_abi_version() != 2:
             raise RuntimeError("libgi2d.so ABI version mismatch")
         _lib = L
     return _lib

@@ -19,6 +19,7 @@
 // preceding blocks' digit counts, and scatters.  Stability + ascending-gid emission order gives the per-tile
 // ascending-gid order the reference gets from cub (quirk Q2).  All of this is HBM/L2-bound integer work.
 #include "gi2d_common.cuh"
+#include "gi2d.h"
 #include <cooperative_groups.h>
 #include <mutex>
 #include <stdlib.h>
@@ -168,6 +169,26 @@ __device__ __forceinline__ void gaussian_bbox(const float *__restrict__ xys, con
     if (w <= 0) { w = 1; area = 0; }
 }
 
+// Optional extras of the fused chain (gi2d_bin_fused_ex): a STICKY status pair that only the host clears -- [0] = largest
+// intersection count seen, [1] |= overflow -- so that a caller replaying a captured graph can poll now and then instead of
+// after every launch; and the (N,12) gradient rows of the backward pass zero-filled by the kernel that walks every Gaussian
+// anyway (instead of a memset node in front of the backward rasterizer).
+struct FusedExtras {
+    int *sticky;
+    float4 *zero_g12;
+};
+__device__ __forceinline__ void publish_sticky(int *sticky, int total, int over) {
+    if (!sticky) return;
+    atomicMax(sticky, total);
+    if (over) atomicOr(sticky + 1, 1);
+}
+__device__ __forceinline__ void zero_grad_row(float4 *zero_g12, int i, int N) {
+    if (zero_g12 && i < N) {
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        zero_g12[3 * (size_t)i] = z; zero_g12[3 * (size_t)i + 1] = z; zero_g12[3 * (size_t)i + 2] = z;
+    }
+}
+
 // Inclusive int32 scan of num_tiles_hit (utils.py:116) -> cum (may be null) and the total in ctl[CTL_N].
 // FUSED additionally emits the compact (tile, gid) pairs and the digit histograms, presets tile_bins to
 // (INT_MAX, 0) for the atomicMin/Max of the last sort pass and writes status_out = {n_isect, overflow}.
@@ -177,7 +198,8 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
                                                       uint32_t *ctl, uint32_t *scan_state, const float *__restrict__ xys,
                                                       const int *__restrict__ radii, int TX, int TY, int capacity,
                                                       uint32_t *keys_out, int *vals_out, PassPlan plan,
-                                                      int2 *tile_bins_init, int n_bins, int *status_out, volatile int *status_host, int use_ticket, int dbg, int wy0, int wy1) {
+                                                      int2 *tile_bins_init, int n_bins, int *status_out, volatile int *status_host, int use_ticket, int dbg, int wy0, int wy1,
+                                                      FusedExtras ex = FusedExtras{nullptr, nullptr}) {
     __shared__ int s_warp[SCAN_T / 32];
     __shared__ int s_bcast[2];
     __shared__ uint32_t s_hist[FUSED ? MAX_PASSES * RADIX : 1];
@@ -191,6 +213,7 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
     const int vbid = use_ticket ? s_bcast[0] : (int)blockIdx.x;
     const int i = vbid * SCAN_T + tid;
     int cnt = i < N ? __ldg(num_tiles_hit + i) : 0;
+    if (FUSED) zero_grad_row(ex.zero_g12, i, N);
     int x0 = 0, w = 1, y0 = 0, area = 0;
     const bool windowed = FUSED && (wy0 > 0 || wy1 < TY);
     if (windowed && cnt > 0) {              // row-sharded render: only the tile rows [wy0, wy1) of this rank count
@@ -213,6 +236,7 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(int N, const int *__restri
             const int over = total > capacity ? 1 : 0;
             ctl[CTL_OVERFLOW] = (uint32_t)over;
             if (status_out) { status_out[0] = total; status_out[1] = over; }
+            publish_sticky(ex.sticky, total, over);
             if (status_host) {          // mapped pinned host memory: the host polls [0] (preset to -1) instead of synchronising
                 status_host[1] = over;
                 __threadfence_system();
@@ -489,6 +513,7 @@ struct SmallArgs {
     volatile int *status_host;
     int dbg;                  // experiments: stop after phase 1 / 2 / 3 (bits 8 / 16 / 32)
     unsigned int *bar;        // {arrival count, generation}: library-owned, zero once, left zero-count by every barrier; null = cg grid.sync
+    FusedExtras ex;
 };
 
 // Grid-wide barrier of a co-resident (cooperatively launched) grid on two words of ordinary device memory: sense reversal,
@@ -562,6 +587,7 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
     // every load of the kernel's input is issued here, independent of the others; the record fields are only consumed
     // in phase 4, their latency hides behind phases 1-3
     float rx = 0.f, ry = 0.f, ro = 0.f, rcx = 0.f, rcy = 0.f, rcz = 0.f, rr = 0.f, rg = 0.f, rb = 0.f;
+    zero_grad_row(a.ex.zero_g12, i, a.N);
     if (i < a.N) {
         const size_t g = (size_t)i;
         const int nth = __ldg(a.nth + i), rad = __ldg(a.radii + i);
@@ -712,6 +738,7 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
         a.ctl[CTL_N] = (uint32_t)block_total;
         a.ctl[CTL_OVERFLOW] = (uint32_t)over;
         if (a.status_out) { a.status_out[0] = block_total; a.status_out[1] = over; }
+        publish_sticky(a.ex.sticky, block_total, over);
         if (a.status_host) {
             a.status_host[1] = over;
             __threadfence_system();
@@ -933,6 +960,7 @@ struct ScatterArgs {
     float4 *packed;
     int *status_out;
     volatile int *status_host;
+    FusedExtras ex;
 };
 
 __device__ __forceinline__ void scatter_rect(const ScatterArgs &a, int i, int &cnt, int &x0, int &w, int &y0) {
@@ -951,6 +979,7 @@ __global__ void __launch_bounds__(256) tile_count_scatter_kernel(ScatterArgs a) 
     const int i = blockIdx.x * 256 + threadIdx.x;
     int cnt, x0, w, y0;
     scatter_rect(a, i, cnt, x0, w, y0);
+    if (!SCATTER) zero_grad_row(a.ex.zero_g12, i, a.N);
     if (!SCATTER && i < a.N && cnt > 0) {
         // The record of this Gaussian as ONE 48-byte row (coalesced reads here): the sort pass then gathers 3 x 16 bytes
         // per intersection instead of nine scalars from four arrays (five 32-byte sectors for 36 useful bytes).
@@ -1000,6 +1029,7 @@ __global__ void __launch_bounds__(NT) tile_scan_kernel(ScatterArgs a, int use_ti
         a.ctl[CTL_N] = (uint32_t)total;
         a.ctl[CTL_OVERFLOW] = (uint32_t)over;
         if (a.status_out) { a.status_out[0] = total; a.status_out[1] = over; }
+        publish_sticky(a.ex.sticky, total, over);
         if (a.status_host) {
             a.status_host[1] = over;
             __threadfence_system();
@@ -1082,7 +1112,8 @@ __global__ void __launch_bounds__(256) tile_sort_pack_kernel(ScatterArgs a) {
 __global__ void __launch_bounds__(256) repack_kernel(int capacity, const int *__restrict__ gids_sorted, const int *__restrict__ status,
                                                       const float *__restrict__ xys, const float *__restrict__ conics,
                                                       const float *__restrict__ colors, const float *__restrict__ opac,
-                                                      float4 *__restrict__ packed) {
+                                                      float4 *__restrict__ packed, int N = 0, float4 *zero_g12 = nullptr) {
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < N; i += gridDim.x * 256) zero_grad_row(zero_g12, i, N);
     const int n = min(__ldg(status), capacity);
     for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
         const int v = __ldg(gids_sorted + i);
@@ -1202,33 +1233,12 @@ int gi2d_tile_bins(int n, const long long *isect_ids_sorted, int n_bins, int *ti
 
 // ---- fused, sync-free chain ---------------------------------------------------------------------------------------
 
-// Number of kernels gi2d_bin_fused launches for this shape on the current device (1 = the one-kernel path; otherwise the
-// scan kernel + one onesweep pass per 8 tile-id bits); the zero-fill of the chain's control block is a memset, not a kernel.
-// Barrier words of the one-kernel path: a pool of 64 pairs per device, allocated and zeroed at the first call outside a
-// stream capture; a stream always maps to the same pair (work on one stream is serial, so a pair is not shared by two
-// grids unless two streams collide in the pool AND run this kernel at the same moment -- it occupies nearly every SM).
-// GI2D_OWN_BARRIER=0, or a first call inside a capture, falls back to cooperative-groups' grid.sync().
+// Barrier words of the one-kernel path: every launch gets its own library-owned pair (gi2d_common.cuh: sync_slot), so two
+// grids of this kernel running at the same moment -- two streams, two graphs replayed side by side -- never share a barrier.
+// GI2D_OWN_BARRIER=0, or no pair available, falls back to cooperative-groups' grid.sync().
 static unsigned int *small_barrier(cudaStream_t stream) {
     static const int own = env_int("GI2D_OWN_BARRIER", 1);
-    if (!own) return nullptr;
-    static unsigned int *pool[16] = {nullptr};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 16) return nullptr;
-    static std::mutex init_lock;                      // ctypes releases the GIL: two host threads may get here together
-    std::lock_guard<std::mutex> guard(init_lock);
-    if (!pool[dev]) {
-        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-        if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) {
-            cudaGetLastError();
-            return nullptr;
-        }
-        unsigned int *p = nullptr;
-        if (cudaMalloc(&p, 64 * 256) != cudaSuccess || cudaMemset(p, 0, 64 * 256) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-        pool[dev] = p;
-    }
-    const uintptr_t h = reinterpret_cast<uintptr_t>(stream);
-    return pool[dev] + 64 * ((h >> 4 ^ h >> 12 ^ h >> 20) & 63);      // 256-byte slots
+    return own ? sync_slot(stream) : nullptr;
 }
 
 // GI2D_SCATTER_BIN: 0 = never, 1 (default) = images of more than 4096 tiles, 2 = whenever the one-kernel path does not apply
@@ -1237,6 +1247,8 @@ static bool use_scatter(int T) {
     return mode == 2 || (mode == 1 && T > 4096);
 }
 
+// Number of kernels gi2d_bin_fused launches for this shape on the current device (1 = the one-kernel path; otherwise the
+// scan kernel + one onesweep pass per 8 tile-id bits); the zero-fill of the chain's control block is a memset, not a kernel.
 int gi2d_bin_fused_kernel_count(int N, int TX, int TY) {
     if (N <= 0 || TX <= 0 || TY <= 0) return 0;
     const int T = TX * TY;
@@ -1257,10 +1269,10 @@ size_t gi2d_bin_fused_workspace_bytes(int N, int TX, int TY, int capacity) {
 //   tile_bins (TX*TY,2) int32: [lo,hi) per tile; EMPTY tiles hold (INT_MAX, 0) until gi2d_raster_sum_fwd_packed
 //   rewrites them to the reference's (0, 0).
 // Precondition (2D path): depths are all zero, so the key is the tile id alone.
-int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
-                               const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
-                               int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
-                               int *status_out, int *status_host, cudaStream_t stream) {
+static int bin_fused_impl(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
+                          const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
+                          int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
+                          int *status_out, int *status_host, FusedExtras ex, cudaStream_t stream) {
     if (N <= 0 || TX <= 0 || TY <= 0 || capacity <= 0 || ty_begin < 0 || ty_end > TY || ty_begin >= ty_end) return GI2D_ERR_INVALID;
     const int T = TX * TY;
     const FusedLayout L = fused_layout(N, T, capacity);
@@ -1282,7 +1294,7 @@ int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, 
             SmallArgs a{N, TX, TY, T, capacity, xys, radii, num_tiles_hit, conics, colors, opacities,
                         reinterpret_cast<uint32_t *>(base + L.mat), reinterpret_cast<uint32_t *>(base + L.mat) + (size_t)((N + 255) / 256) * sp.tp,
                         ctl, gids_sorted, tile_bins, reinterpret_cast<float4 *>(packed), status_out, status_host, dbg,
-                        small_barrier(stream)};
+                        small_barrier(stream), ex};
             void *args[] = {&a};
             const cudaError_t e = cudaLaunchCooperativeKernel(sp.fn, dim3((N + sp.nt - 1) / sp.nt), dim3(sp.nt), args, sp.smem, stream);
             return e == cudaSuccess ? GI2D_OK : GI2D_ERR_CUDA_BASE + (int)e;
@@ -1294,7 +1306,7 @@ int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, 
         ScatterArgs a{N, TX, TY, T, capacity, ty_begin, ty_end, xys, radii, num_tiles_hit, conics, colors, opacities,
                       reinterpret_cast<uint32_t *>(base + L.tile_cur), reinterpret_cast<float4 *>(base + L.rows),
                       reinterpret_cast<uint32_t *>(base + L.tile_state), ctl,
-                      gids_sorted, tile_bins, reinterpret_cast<float4 *>(packed), status_out, status_host};
+                      gids_sorted, tile_bins, reinterpret_cast<float4 *>(packed), status_out, status_host, ex};
         const int gblocks = (N + 255) / 256, sblocks = (T + 1023) / 1024;
         tile_count_scatter_kernel<false><<<gblocks, 256, 0, stream>>>(a);
         tile_scan_kernel<1024><<<sblocks, 1024, 0, stream>>>(a, all_resident(tile_scan_kernel<1024>, 1024, sblocks) ? 0 : 1);
@@ -1315,7 +1327,7 @@ int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, 
         const int ticket = all_resident(scan_kernel<true, NT>, NT, grid) ? 0 : 1;                                          \
         scan_kernel<true, NT><<<grid, NT, 0, stream>>>(N, num_tiles_hit, nullptr, ctl, scan_state, xys, radii, TX, TY,     \
                                                        capacity, k0, v0, plan, bins2, T, status_out, status_host, ticket, dbg,        \
-                                                       ty_begin, ty_end);                                                 \
+                                                       ty_begin, ty_end, ex);                                             \
     }
     if (tn.scan_t == 256) GI2D_SCAN(256) else if (tn.scan_t == 512) GI2D_SCAN(512) else GI2D_SCAN(1024)
 #undef GI2D_SCAN
@@ -1350,6 +1362,24 @@ int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, 
     return cuda_status();
 }
 
+int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
+                               const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
+                               int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
+                               int *status_out, int *status_host, cudaStream_t stream) {
+    return bin_fused_impl(N, TX, TY, ty_begin, ty_end, xys, radii, num_tiles_hit, conics, colors, opacities, capacity, ws, ws_bytes,
+                          gids_sorted, tile_bins, packed, status_out, status_host, FusedExtras{nullptr, nullptr}, stream);
+}
+
+// gi2d_bin_fused_rows_notify with the optional extras of struct gi2d_bin_args (include/gi2d.h): a sticky status pair and the
+// zero fill of the backward pass's gradient rows.
+int gi2d_bin_fused_ex(const gi2d_bin_args *a, cudaStream_t stream) {
+    if (!a) return GI2D_ERR_INVALID;
+    if (a->zero_grads12 && (reinterpret_cast<uintptr_t>(a->zero_grads12) & 15)) return GI2D_ERR_INVALID;
+    return bin_fused_impl(a->N, a->TX, a->TY, a->ty_begin, a->ty_end, a->xys, a->radii, a->num_tiles_hit, a->conics, a->colors,
+                          a->opacities, a->capacity, a->ws, a->ws_bytes, a->gids_sorted, a->tile_bins, a->packed, a->status_out,
+                          a->status_host, FusedExtras{a->status_sticky, reinterpret_cast<float4 *>(a->zero_grads12)}, stream);
+}
+
 int gi2d_bin_fused_rows(int N, int TX, int TY, int ty_begin, int ty_end, const float *xys, const int *radii,
                         const int *num_tiles_hit, const float *conics, const float *colors, const float *opacities,
                         int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
@@ -1367,14 +1397,23 @@ int gi2d_bin_fused(int N, int TX, int TY, const float *xys, const int *radii, co
                                gids_sorted, tile_bins, packed, status_out, stream);
 }
 
+int gi2d_repack_records_ex(int capacity, const int *gids_sorted, const int *status, const float *xys, const float *conics,
+                           const float *colors, const float *opacities, float *packed, int N, float *zero_grads12,
+                           cudaStream_t stream) {
+    if (capacity < 0 || !gids_sorted || !status || !xys || !conics || !colors || !opacities || !packed) return GI2D_ERR_INVALID;
+    if (zero_grads12 && (N <= 0 || (reinterpret_cast<uintptr_t>(zero_grads12) & 15))) return GI2D_ERR_INVALID;
+    if (capacity == 0 && !zero_grads12) return GI2D_OK;
+    const int work = std::max(capacity, zero_grads12 ? N : 0);
+    const int grid = std::min((work + 255) / 256, 8 * 148);
+    repack_kernel<<<grid, 256, 0, stream>>>(capacity, gids_sorted, status, xys, conics, colors, opacities,
+                                            reinterpret_cast<float4 *>(packed), zero_grads12 ? N : 0,
+                                            reinterpret_cast<float4 *>(zero_grads12));
+    return cuda_status();
+}
+
 int gi2d_repack_records(int capacity, const int *gids_sorted, const int *status, const float *xys, const float *conics,
                         const float *colors, const float *opacities, float *packed, cudaStream_t stream) {
-    if (capacity < 0 || !gids_sorted || !status || !xys || !conics || !colors || !opacities || !packed) return GI2D_ERR_INVALID;
-    if (capacity == 0) return GI2D_OK;
-    const int grid = std::min((capacity + 255) / 256, 8 * 148);
-    repack_kernel<<<grid, 256, 0, stream>>>(capacity, gids_sorted, status, xys, conics, colors, opacities,
-                                            reinterpret_cast<float4 *>(packed));
-    return cuda_status();
+    return gi2d_repack_records_ex(capacity, gids_sorted, status, xys, conics, colors, opacities, packed, 0, nullptr, stream);
 }
 
 }  // extern "C"

@@ -129,4 +129,11 @@ __device__ __forceinline__ float2 record_extent(float cx, float cy, float cz, fl
     return make_float2(ex, ey);
 }
 
+// Library-owned pairs of device words {count, generation} for self-cleaning device-side protocols (grid barrier of the
+// one-kernel binning, last-block ticket of the projection total): zeroed once per device, left zero by every user.  Every
+// launch gets its OWN pair: eager launches cycle through a ring (a pair is long idle again when the ring wraps), launches
+// recorded into a CUDA graph -- which replay at any later time, on any stream -- get a pair that is never handed out again.
+// nullptr when no pair can be provided (pool not yet created and the stream is capturing, or the capture pairs are spent).
+unsigned int *sync_slot(cudaStream_t stream);
+
 }  // namespace gi2d

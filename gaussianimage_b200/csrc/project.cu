@@ -65,7 +65,8 @@ __global__ void __launch_bounds__(PB) project_fwd_kernel(int N, const float *__r
                                                          const float *__restrict__ p1, float hw, float hh, int TX,
                                                          int TY, float *__restrict__ xys, float *__restrict__ depths,
                                                          int *__restrict__ radii, float *__restrict__ conics,
-                                                         int *__restrict__ num_tiles_hit) {
+                                                         int *__restrict__ num_tiles_hit, unsigned int *total_slot = nullptr,
+                                                         int *total_dev = nullptr, volatile int *total_host = nullptr) {
     __shared__ __align__(16) float s3[PB * 3];
     const int base = blockIdx.x * PB, tid = threadIdx.x, i = base + tid;
     const int nb = min(PB, N - base);
@@ -111,6 +112,29 @@ __global__ void __launch_bounds__(PB) project_fwd_kernel(int N, const float *__r
     s3[3 * tid] = conic.x; s3[3 * tid + 1] = conic.y; s3[3 * tid + 2] = conic.z;
     __syncthreads();
     stage_out3<VEC>(s3, conics, base, nb);
+    // The intersection total (what compute_cumulative_intersects' `.item()` reads, utils.py:116-118) as a by-product: block
+    // sums meet in a library-owned word, the last block to arrive publishes the total -- to device memory and/or to a MAPPED
+    // PINNED HOST word the host can poll without a stream synchronisation -- and leaves the pair of words zero again.
+    if (total_slot) {
+        __shared__ int s_sum[PB / 32];
+        const int w = __reduce_add_sync(0xffffffffu, tiles);
+        if ((tid & 31) == 0) s_sum[tid >> 5] = w;
+        __syncthreads();
+        if (tid == 0) {
+            int b = 0;
+#pragma unroll
+            for (int k = 0; k < PB / 32; ++k) b += s_sum[k];
+            atomicAdd(total_slot, (unsigned int)b);
+            __threadfence();
+            if (atomicAdd(total_slot + 1, 1u) == gridDim.x - 1) {
+                __threadfence();
+                const int total = (int)atomicExch(total_slot, 0u);
+                total_slot[1] = 0u;
+                if (total_dev) *total_dev = total;
+                if (total_host) { __threadfence_system(); *total_host = total; }
+            }
+        }
+    }
 }
 
 // reference helpers.cuh:71-82 cov2d_to_conic_vjp: V = -X G X, v_cov2d = (V00, V10+V01, V11).
@@ -325,6 +349,32 @@ int gi2d_project_scale_rot_fwd(int N, const float *means2d, const float *scales2
         project_fwd_kernel<1, true><<<grid, PB, 0, stream>>>(N, means2d, nullptr, scales2d, rotation, hw, hh, TX, TY, xys, depths, radii, conics, num_tiles_hit);
     else
         project_fwd_kernel<1, false><<<grid, PB, 0, stream>>>(N, means2d, nullptr, scales2d, rotation, hw, hh, TX, TY, xys, depths, radii, conics, num_tiles_hit);
+    return cuda_status();
+}
+
+// Either projection, additionally publishing the total of num_tiles_hit (see the kernel): total_dev (device int) and / or
+// total_host (mapped pinned host int, preset by the caller to a negative value and polled) may be NULL.
+int gi2d_project_fwd_total(int mode, int N, const float *means2d, const float *p_a, const float *p_b, int H, int W, int TX, int TY,
+                           float *xys, float *depths, int *radii, float *conics, int *num_tiles_hit, int *total_dev,
+                           int *total_host, cudaStream_t stream) {
+    if (N < 0 || H <= 0 || W <= 0 || (mode != 0 && mode != 1)) return GI2D_ERR_INVALID;
+    if (N == 0) {
+        if (total_dev) cudaMemsetAsync(total_dev, 0, sizeof(int), stream);
+        if (total_host) *reinterpret_cast<volatile int *>(total_host) = 0;
+        return cuda_status();
+    }
+    unsigned int *slot = (total_dev || total_host) ? sync_slot(stream) : nullptr;
+    if ((total_dev || total_host) && !slot) return GI2D_ERR_INVALID;
+    const float hw = (float)(unsigned)W * 0.5f, hh = (float)(unsigned)H * 0.5f;
+    const int grid = (N + PB - 1) / PB;
+    const bool vec = aligned16(means2d) && aligned16(p_a) && aligned16(xys) && aligned16(conics);
+    if (mode == 0) {
+        if (vec) project_fwd_kernel<0, true><<<grid, PB, 0, stream>>>(N, means2d, p_a, nullptr, nullptr, hw, hh, TX, TY, xys, depths, radii, conics, num_tiles_hit, slot, total_dev, total_host);
+        else project_fwd_kernel<0, false><<<grid, PB, 0, stream>>>(N, means2d, p_a, nullptr, nullptr, hw, hh, TX, TY, xys, depths, radii, conics, num_tiles_hit, slot, total_dev, total_host);
+    } else {
+        if (vec) project_fwd_kernel<1, true><<<grid, PB, 0, stream>>>(N, means2d, nullptr, p_a, p_b, hw, hh, TX, TY, xys, depths, radii, conics, num_tiles_hit, slot, total_dev, total_host);
+        else project_fwd_kernel<1, false><<<grid, PB, 0, stream>>>(N, means2d, nullptr, p_a, p_b, hw, hh, TX, TY, xys, depths, radii, conics, num_tiles_hit, slot, total_dev, total_host);
+    }
     return cuda_status();
 }
 

@@ -846,6 +846,20 @@ int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *t
     return cuda_status();
 }
 
+// gi2d_raster_sum_bwd_packed[_scaled] WITHOUT the zero fill: `grads12` was zeroed by the binning chain of the forward pass
+// (gi2d_bin_fused_ex / gi2d_repack_records_ex: zero_grads12), so no memset node sits in front of the kernel.  v_scale may be NULL.
+int gi2d_raster_sum_bwd_packed_acc(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
+                                   const float *v_out, const float *v_scale, float *grads12, cudaStream_t stream) {
+    if (N <= 0 || TX <= 0 || TY <= 0) return GI2D_ERR_INVALID;
+    if (reinterpret_cast<uintptr_t>(grads12) & 15) return GI2D_ERR_INVALID;
+    GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
+    GradOut out{grads12, nullptr, nullptr, nullptr, nullptr};
+    const int ish = bwd_ishift(N, TX * TY);
+    raster_bwd_kernel<true, true><<<bwd_grid(raster_bwd_kernel<true, true>, (TX * TY) << ish), BW_THREADS, BW_SMEM, stream>>>(
+        TX, W, H, TX * TY, ish, tile_bins, reinterpret_cast<const float4 *>(packed), src, v_out, out, vec_ok(W, v_out), v_scale);
+    return cuda_status();
+}
+
 // Loss epilogue: forward over the packed records that ends in the L2 loss the reference's training step
 // computes from the image (gaussianimage_cholesky.py:84-85 clamp + layout change, utils.py:20-25 F.mse_loss), and writes
 // d loss / d out_img into v_out for gi2d_raster_sum_bwd_packed_scaled.  The image itself is optional.

@@ -66,5 +66,5 @@ def decode_project_gaussians_2d(xyz: Tensor, quant_cholesky_elements: Tensor, sc
                                                      int(idx.dtype == torch.int64), idx.size(1), cb.size(1), cb.data_ptr(), H, W, TX, TY,
                                                      xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), conics.data_ptr(),
                                                      nth.data_ptr(), colors.data_ptr(), _C._stream(dev)), "decode_project")
-        _tag_zero_depth(depths)        # rasterize_gaussians_sum may take the fused (tile-only sort) path
+        _tag_zero_depth(depths, xys)        # rasterize_gaussians_sum may take the fused (tile-only sort) path
     return xys, depths, radii, conics, nth, colors

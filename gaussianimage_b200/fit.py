@@ -24,7 +24,7 @@ from .optimizer import Adan
 
 class GraphFitter:
     def __init__(self, gt_chw: torch.Tensor, num_points: int, lr: float = 0.018, seed: int = 1, fused: bool = True,
-                 lr_step: int = 20000, lr_gamma: float = 0.5):
+                 lr_step: int = 20000, lr_gamma: float = 0.5, check_every: int = 256):
         assert gt_chw.dim() == 4 and gt_chw.shape[:2] == (1, 3) and gt_chw.is_cuda
         dev = gt_chw.device
         self.H, self.W = int(gt_chw.shape[2]), int(gt_chw.shape[3])
@@ -45,6 +45,8 @@ class GraphFitter:
         self._state = None if fused else [[torch.zeros_like(p) for p in self.params] for _ in range(4)]   # m, v, d, neg_pre_grad
         self.loss = None
         self.graph = None
+        self.check_every = check_every      # replays between two reads of the sticky overflow status (0 = never)
+        self.recaptures = 0
 
     # one training iteration, eager
     def step(self):
@@ -117,11 +119,28 @@ class GraphFitter:
                 self.opt.param_groups[0]["lr"] = self.lr0 * self.lr_gamma ** (self.iteration // self.lr_step)
                 self.opt.sync_hyperparameters()
             if self.graph is not None:
+                if self.check_every and self.iteration % self.check_every == 0:
+                    self._check_overflow()
                 self.graph.replay()
             else:
                 self.step()
             self.iteration += 1
+        if self.graph is not None and self.check_every:
+            self._check_overflow()
         return self.loss
+
+    def _check_overflow(self):
+        """A replayed graph cannot grow its workspace: as the Gaussians spread, the intersection count may outgrow the capacity
+        frozen at capture time.  The binning chain reports that in a sticky device word; read it now and then, and on
+        overflow -- the capacity has been raised by check_overflow() -- capture the step again.  (The replays since the
+        overflow saw truncated tile lists: at most `check_every` slightly wrong gradient steps, then exact again.)"""
+        from .rasterize_sum import check_overflow
+        try:
+            check_overflow(self.gt.device)
+        except RuntimeError:
+            self.recaptures += 1
+            self.graph = None
+            self.capture()
 
     def psnr(self) -> float:
         """gaussianimage_cholesky.py:118-119 (for the L2 loss, mse_loss(image, gt) is the loss itself)."""

@@ -14,10 +14,19 @@ from . import cuda as _C
 from ._lib import cpp_autograd
 
 
-def _tag_zero_depth(depths: Tensor) -> None:
+_generation = 0
+
+
+def _tag_zero_depth(depths: Tensor, xys: Tensor = None) -> None:
     """Both 2D projections write depths == 0 (foward2d.cu:67,122); remember that on the tensor object so that
-    rasterize_gaussians_sum can sort on the tile bits alone (quirk Q2) without inspecting the data."""
+    rasterize_gaussians_sum can sort on the tile bits alone (quirk Q2) without inspecting the data.  xys additionally gets
+    the generation number of this projection call: the binning memo only ever matches tensors that carry the generation
+    it was recorded for (never a buffer that merely has the same address and version counter)."""
+    global _generation
     depths._gi2d_zero_depth_version = depths._version
+    if xys is not None:
+        _generation += 1
+        xys._gi2d_gen = _generation
 
 
 def project_gaussians_2d(
@@ -37,7 +46,7 @@ def project_gaussians_2d(
     if T is not None:               # the same operator as a C++ autograd Function (csrc/torch_glue.cpp: ProjectFn)
         out = T.project_autograd(0, means2d.contiguous(), L_elements.contiguous(), None, img_height, img_width,
                                  tile_bounds[0], tile_bounds[1])
-        _tag_zero_depth(out[1])
+        _tag_zero_depth(out[1], out[0])
         return tuple(out)
     return _ProjectGaussians2d.apply(
         means2d.contiguous(), L_elements.contiguous(), img_height, img_width, tile_bounds, clip_thresh
@@ -55,7 +64,7 @@ class _ProjectGaussians2d(Function):
         ctx.save_for_backward(means2d, L_elements, radii, conics)
         ctx.mark_non_differentiable(radii, num_tiles_hit)
         ctx.set_materialize_grads(False)      # v_depths etc. arrive as None instead of freshly filled zero tensors
-        _tag_zero_depth(depths)
+        _tag_zero_depth(depths, xys)
         return xys, depths, radii, conics, num_tiles_hit
 
     @staticmethod

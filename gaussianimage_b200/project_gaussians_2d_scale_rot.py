@@ -28,7 +28,7 @@ def project_gaussians_2d_scale_rot(
     if T is not None and means2d.shape[-2] >= 1 and means2d.shape[-1] == 2:     # else: the ValueError of the Python Function
         out = T.project_autograd(1, means2d.contiguous(), scales2d.contiguous(), rotation.contiguous(), img_height, img_width,
                                  tile_bounds[0], tile_bounds[1])
-        _tag_zero_depth(out[1])
+        _tag_zero_depth(out[1], out[0])
         return tuple(out)
     return _ProjectGaussians2dScaleRot.apply(
         means2d.contiguous(), scales2d.contiguous(), rotation.contiguous(), img_height, img_width, tile_bounds, clip_thresh
@@ -48,7 +48,7 @@ class _ProjectGaussians2dScaleRot(Function):
         ctx.save_for_backward(means2d, scales2d, rotation, radii, conics)
         ctx.mark_non_differentiable(radii, num_tiles_hit)
         ctx.set_materialize_grads(False)
-        _tag_zero_depth(depths)
+        _tag_zero_depth(depths, xys)
         return xys, depths, radii, conics, num_tiles_hit
 
     @staticmethod

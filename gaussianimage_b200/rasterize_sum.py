@@ -23,34 +23,82 @@ from torch import Tensor
 from torch.autograd import Function
 
 from . import cuda as _C
-from ._lib import check, cpp_autograd, glue, lib
+import ctypes as C
+
+from ._lib import BinArgs, check, cpp_autograd, glue, lib
 from .utils import _depths_known_zero, bin_and_sort_gaussians, compute_cumulative_intersects
 
 _sync_free = os.environ.get("GI2D_SYNC_FREE", "0") == "1"
-_capacity: dict = {}        # (device index, N, TX, TY) -> intersection capacity of the fused workspace
+_capacity: dict = {}        # (device index, N, TX, TY) -> intersection capacity of the fused workspace (Python Functions)
 _last_status: dict = {}     # device index -> (scratch, status offset, capacity, key) of the most recent fused call
+_sticky: dict = {}          # (device index, N, TX, TY) -> int32[2] device {max n_isect seen, overflowed}: only the host clears it
 
 
 def set_sync_free(flag: bool) -> None:
     """True: never read the intersection count back (graph-capturable, maximum throughput); the caller is expected
-    to call `check_overflow()` now and then.  False (default): strict mode, one read-back at the end of forward."""
+    to call `check_overflow()` now and then.  False (default): strict mode -- the workspace is sized from the intersection
+    total (C++ operators: published by the projection kernel; Python Functions: read back once at the end of forward)."""
     global _sync_free
     _sync_free = bool(flag)
+    T = glue()
+    if T is not None:
+        T.set_sync_free(_sync_free)
+
+
+def get_capacity(device_index: int, N: int, TX: int, TY: int) -> int:
+    """Learned intersection capacity of this shape (0 = none yet) -- what sync-free / captured calls allocate."""
+    T = cpp_autograd()
+    c = T.get_capacity(device_index, N, TX, TY) if T is not None else 0
+    return max(c, _capacity.get((device_index, N, TX, TY), 0))
+
+
+def set_capacity(device_index: int, N: int, TX: int, TY: int, cap: int) -> None:
+    _capacity[(device_index, N, TX, TY)] = int(cap)
+    T = glue()
+    if T is not None:
+        T.set_capacity(device_index, N, TX, TY, int(cap))
+
+
+def _overflowed(n: int, cap: int):
+    raise RuntimeError(f"gi2d: {n} tile intersections exceeded the workspace capacity {cap}; "
+                       "the capacity has been raised, re-run the step")
 
 
 def check_overflow(device=None) -> int:
-    """Synchronising check of the most recent fused forward on `device`; returns its intersection count and raises
-    if it did not fit the workspace (results of that call were truncated)."""
+    """Synchronising check of `device`: the most recent fused forward AND the sticky status of every shape that ran
+    sync-free or inside a replayed CUDA graph since the last check (a replay overwrites the per-call status; the sticky
+    pair is only ever cleared here).  Returns the intersection count of the most recent call; raises if anything did not
+    fit its workspace (those results were truncated) -- after raising the capacity of that shape and dropping the memoised
+    binning, so that simply re-running (re-capturing) the step is correct."""
     idx = torch.cuda.current_device() if device is None else torch.device(device).index
-    if idx not in _last_status:
-        return 0
-    scratch, o_status, cap, key = _last_status[idx]
-    n, over = scratch[o_status:o_status + 8].view(torch.int32).tolist()
-    if over:
-        _capacity[key] = max(_capacity.get(key, 0), int(n * 1.25) + 1024)
-        raise RuntimeError(f"gi2d: {n} tile intersections exceeded the workspace capacity {cap}; "
-                           "the capacity has been raised, re-run the step")
-    return int(n)
+    n_last = 0
+    T = glue()
+    if T is not None:
+        n_last, over, n_over, cap = T.check_overflow(idx)
+        if over:
+            _geometry.clear()
+            _overflowed(n_over, cap)
+    for key, st in list(_sticky.items()):
+        if key[0] != idx:
+            continue
+        n, over = st.tolist()
+        if over:
+            cap = _capacity.get(key, 0)
+            _capacity[key] = max(cap, int(n * 1.25) + 1024)
+            st.zero_()
+            _geometry.clear()
+            _last_status.pop(idx, None)
+            _overflowed(n, cap)
+    if idx in _last_status:
+        scratch, o_status, cap, key = _last_status[idx]
+        n, over = scratch[o_status:o_status + 8].view(torch.int32).tolist()
+        if over:
+            _capacity[key] = max(_capacity.get(key, 0), int(n * 1.25) + 1024)
+            _geometry.clear()
+            _last_status.pop(idx, None)
+            _overflowed(n, cap)
+        n_last = int(n) if not n_last else n_last
+    return int(n_last)
 
 
 def rasterize_gaussians_sum(
@@ -85,12 +133,16 @@ def rasterize_gaussians_sum(
         raise ValueError("colors must have dimensions (N, D)")
     T = cpp_autograd()
     if (T is not None and (BLOCK_H, BLOCK_W) == (16, 16) and colors.shape[-1] == 3 and xys.is_cuda
-            and xys.dtype == torch.float32 and _depths_known_zero(depths)):
-        r = _fused_cpp(T, xys.contiguous(), radii.contiguous(), conics.contiguous(), num_tiles_hit.contiguous(),
-                       colors.contiguous(), opacity.contiguous(), background.contiguous(), int(img_height), int(img_width),
-                       return_alpha)
-        if r is not None:
-            return r
+            and xys.dtype == torch.float32):
+        # the whole fused path as ONE call into the host glue (csrc/torch_glue.cpp: rasterize); an empty result = these are
+        # not the unmodified outputs of one of our projections -> the reference's staged sequence below
+        if background.device != xys.device:
+            background = background.to(xys.device)
+        r = T.rasterize(xys.contiguous(), depths.contiguous(), radii.contiguous(), conics.contiguous(), num_tiles_hit.contiguous(),
+                        colors.contiguous(), opacity.contiguous(), background.contiguous(), int(img_height), int(img_width),
+                        bool(return_alpha))
+        if r:
+            return (r[0], r[1]) if return_alpha else r[0]
     return _RasterizeGaussiansSum.apply(
         xys.contiguous(), depths.contiguous(), radii.contiguous(), conics.contiguous(), num_tiles_hit.contiguous(),
         colors.contiguous(), opacity.contiguous(), img_height, img_width, BLOCK_H, BLOCK_W, background.contiguous(),
@@ -232,7 +284,7 @@ class FusedResult:
 
 
 def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap, want_aux=False, host_slot=-1,
-                raster=None):
+                raster=None, sticky=None):
     """One asynchronous pass of the fused chain (csrc/binning.cu gi2d_bin_fused + csrc/raster.cu packed forward) on the
     current stream with an intersection capacity `cap`.  Returns a FusedResult: out_img, final_Ts/final_idx (or None),
     tile_bins (T,2), packed (cap*12), gids_sorted (cap), status (2,) = [n, overflow].  host_slot >= 0 also publishes the
@@ -242,7 +294,7 @@ def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, 
         r = FusedResult()
         (r.out_img, r.final_Ts, r.final_idx, r.tile_bins, r.packed, r._scratch, r._o_gids, r._o_status) = T.fused_forward(
             xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap,
-            _host_status.base + 8 * host_slot if host_slot >= 0 else 0, bool(want_aux))
+            _host_status.base + 8 * host_slot if host_slot >= 0 else 0, bool(want_aux), 0 if sticky is None else sticky.data_ptr())
         r._cap = cap
         return r
     dev = xys.device
@@ -261,10 +313,10 @@ def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, 
     r.packed = packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
     base = scratch.data_ptr()
     host_ptr = _host_status.base + 8 * host_slot if host_slot >= 0 else 0
-    check(L.gi2d_bin_fused_rows_notify(N, TX, TY, 0, TY, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(),
-                                       conics.data_ptr(), colors.data_ptr(), opacity.data_ptr(), cap, base, ws_bytes,
-                                       base + o_gids, tile_bins.data_ptr(), packed.data_ptr(), base + o_status, host_ptr,
-                                       stream), "bin_fused")
+    a = BinArgs(N, TX, TY, 0, TY, cap, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(), conics.data_ptr(),
+                colors.data_ptr(), opacity.data_ptr(), base, ws_bytes, base + o_gids, tile_bins.data_ptr(), packed.data_ptr(),
+                base + o_status, host_ptr or None, None if sticky is None else sticky.data_ptr(), None)
+    check(L.gi2d_bin_fused_ex(C.byref(a), stream), "bin_fused")
     if raster is not None:                 # another consumer of the lists (loss.py: forward that ends in the loss)
         r.out_img = r.final_Ts = r.final_idx = None
         raster(r, base + o_status, stream)
@@ -283,10 +335,13 @@ class _Geometry:
     again with the SAME xys / radii / num_tiles_hit tensors (same storage, same version counters -- the reference model
     does it three times per forward, gaussianimage_cholesky.py:81,89,95, quirk Q13) only rebuilds the packed records from
     the new conics / colours / opacities (gi2d_repack_records) and rasterizes; the lists are bit-identical by construction."""
-    __slots__ = ("xys", "radii", "nth", "versions", "shape", "result", "cap", "n_isect")
+    __slots__ = ("xys", "radii", "nth", "versions", "shape", "result", "cap", "n_isect", "gen", "captured")
 
     def matches(self, xys, radii, nth, shape):
-        return (self.shape == shape and self.xys.data_ptr() == xys.data_ptr() and self.radii.data_ptr() == radii.data_ptr()
+        # only tensors TAGGED by one of this package's projections (a generation number set where they were produced) can match:
+        # a buffer somebody re-filled through a raw pointer has no tag of the same generation, whatever its address and version
+        return (self.gen is not None and getattr(xys, "_gi2d_gen", None) == self.gen and self.shape == shape
+                and self.xys.data_ptr() == xys.data_ptr() and self.radii.data_ptr() == radii.data_ptr()
                 and self.nth.data_ptr() == nth.data_ptr() and self.versions == (xys._version, radii._version, nth._version))
 
 
@@ -299,7 +354,12 @@ staged_calls = 0           # calls that took the reference's staged sequence (ar
 
 def stats() -> dict:
     """Counters of the operator's dispatch (tests read them): which path the calls took, how often the binning was re-used."""
-    return {"fast_calls": fast_calls, "staged_calls": staged_calls, "geometry_hits": geometry_hits}
+    d = {"fast_calls": fast_calls, "staged_calls": staged_calls, "geometry_hits": geometry_hits}
+    T = glue()
+    if T is not None:
+        for k, v in T.stats().items():
+            d[k] = d.get(k, 0) + v
+    return d
 
 
 def set_memoise_binning(flag: bool):
@@ -307,6 +367,9 @@ def set_memoise_binning(flag: bool):
     global _memoise
     _memoise = bool(flag)
     _geometry.clear()
+    T = glue()
+    if T is not None:
+        T.set_memoise(_memoise)
 
 
 def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=False, raster=None):
@@ -348,9 +411,16 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
     strict = not (_sync_free or torch.cuda.is_current_stream_capturing())
     if strict and _host_status is None:
         _host_status = _HostStatus()
+    capturing = torch.cuda.is_current_stream_capturing()
+    sticky = _sticky.get(key)
+    if sticky is None and not capturing:      # allocated (zeroed) at the first eager call: a capture only ever records its address
+        sticky = _sticky[key] = torch.zeros(2, dtype=torch.int32, device=dev)
     with _C._guard(dev):
         gkey = (dev.index, _C._stream(dev))
         g = _geometry.get(gkey) if _memoise else None
+        if g is not None and g.captured and not capturing:      # recorded inside a capture: its tensors live in that graph's pool
+            _geometry.pop(gkey, None)
+            g = None
         if g is not None and g.matches(xys, radii, nth, key):
             geometry_hits += 1
             r = fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux, raster)
@@ -365,7 +435,8 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
             if cap is None:
                 cap = _capacity[key] = max(4 * N, 1 << 14)
             slot = _host_status.acquire() if strict else -1
-            r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux, slot, raster)
+            r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux, slot, raster,
+                            None if strict else sticky)
             _last_status[dev.index] = (r._scratch, r._o_status, cap, key)
             n = None
             if not strict:
@@ -375,10 +446,11 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
                 ctx.num_intersects = n
                 break
             _capacity[key] = int(n * 1.25) + 1024  # truncated: grow and redo
-        if _memoise:
+        if _memoise and getattr(xys, "_gi2d_gen", None) is not None:
             g = _Geometry()
             g.xys, g.radii, g.nth, g.shape = xys.detach(), radii.detach(), nth.detach(), key   # no autograd graph kept alive
             g.versions = (xys._version, radii._version, nth._version)
+            g.gen, g.captured = xys._gi2d_gen, capturing
             keep = FusedResult()               # lists only: the image is an autograd output and would pin the whole graph
             keep._scratch, keep._o_gids, keep._o_status, keep._cap, keep.tile_bins = r._scratch, r._o_gids, r._o_status, cap, r.tile_bins
             g.result, g.cap, g.n_isect = keep, cap, n
@@ -387,63 +459,6 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
         return r
     ctx.save_for_backward(r.tile_bins, r.packed)
     return r.out_img, r.final_Ts
-
-
-_offsets: dict = {}
-
-
-def _fused_cpp(T, xys, radii, conics, nth, colors, opacity, background, H, W, return_alpha):
-    """_forward_fused with the autograd node in C++ (csrc/torch_glue.cpp: RasterFusedFn): same chain, same strict-mode
-    polling and capacity retry, same memo entry.  Returns None when the binning of these geometry tensors is memoised --
-    the Python Function then re-rasterizes it as before."""
-    global _host_status
-    dev, N = xys.device, xys.size(0)
-    TX, TY = (W + 15) // 16, (H + 15) // 16
-    conics, colors = _C._f32(conics, "conics"), _C._f32(colors, "colors")
-    opacity, background = _C._f32(opacity, "opacity"), _C._f32(background.to(dev), "background")
-    radii, nth = _C._i32(radii, "radii"), _C._i32(nth, "num_tiles_hit")
-    key = (dev.index, N, TX, TY)
-    strict = not (_sync_free or torch.cuda.is_current_stream_capturing())
-    if strict and _host_status is None:
-        _host_status = _HostStatus()
-    gkey = (dev.index, _C._stream(dev))
-    if _memoise:
-        g = _geometry.get(gkey)
-        if g is not None and g.matches(xys, radii, nth, key):
-            return None
-    global fast_calls
-    fast_calls += 1
-    while True:
-        cap = _capacity.get(key)
-        if cap is None:
-            cap = _capacity[key] = max(4 * N, 1 << 14)
-        slot = _host_status.acquire() if strict else -1
-        out_img, final_Ts, _, tile_bins, packed, scratch = T.raster_fused_autograd(
-            xys, radii, conics, nth, colors, opacity, background, H, W, cap,
-            _host_status.base + 8 * slot if slot >= 0 else 0, bool(return_alpha))
-        okey = (N, H, W, cap)
-        off = _offsets.get(okey)
-        if off is None:
-            off = _offsets[okey] = T.fused_offsets(N, H, W, cap)
-        _last_status[dev.index] = (scratch, off[1], cap, key)
-        n = None
-        if not strict:
-            break
-        n, over = _host_status.wait(slot)
-        if not over:
-            break
-        _capacity[key] = int(n * 1.25) + 1024          # truncated: grow and redo
-    if _memoise:
-        g = _Geometry()
-        g.xys, g.radii, g.nth, g.shape = xys.detach(), radii.detach(), nth.detach(), key
-        g.versions = (xys._version, radii._version, nth._version)
-        keep = FusedResult()
-        keep._scratch, keep._o_gids, keep._o_status, keep._cap, keep.tile_bins = scratch, off[0], off[1], cap, tile_bins
-        g.result, g.cap, g.n_isect = keep, cap, n
-        _geometry[gkey] = g
-    if return_alpha:
-        return out_img, 1 - final_Ts
-    return out_img
 
 
 def _forward_staged(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity, background):

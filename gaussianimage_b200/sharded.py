@@ -21,8 +21,10 @@ from typing import List, Optional, Tuple
 import torch
 import torch.distributed as dist
 
+import ctypes as C
+
 from . import cuda as _C
-from ._lib import check, lib
+from ._lib import BinArgs, check, lib
 
 
 def image_shard(num_images: int, rank: int, world: int) -> List[int]:
@@ -68,6 +70,9 @@ class RowShardedRenderer:
         self.background = torch.ones(3, dtype=torch.float32, device=self.device)
         self._cap = None
         self.status = None
+        self._sticky = None          # int32[2] {max intersections seen in this rank's band, overflowed}: cleared only by the host
+        self._frames = 0
+        self.check_every = 64        # frames between two reads of the sticky status once a capacity has proved sufficient
 
     def frame(self) -> torch.Tensor:
         return self.buffer[: self.H]
@@ -94,21 +99,31 @@ class RowShardedRenderer:
                     self._bins = torch.empty((self.TX * self.TY, 2), dtype=torch.int32, device=dev)
                     self._packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
                     self.status = torch.zeros((2,), dtype=torch.int32, device=dev)
+                    self._sticky = torch.zeros((2,), dtype=torch.int32, device=dev)
                     self._ws_cap = cap
-                check(L.gi2d_bin_fused_rows(N, self.TX, self.TY, r0, r1, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(),
-                                            conics.data_ptr(), colors.data_ptr(), opacity.data_ptr(), cap, self._ws.data_ptr(),
-                                            ws_bytes, self._gids.data_ptr(), self._bins.data_ptr(), self._packed.data_ptr(),
-                                            self.status.data_ptr(), stream), "bin_fused_rows")
+                    self._cap_checked = False
+                a = BinArgs(N, self.TX, self.TY, r0, r1, cap, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(),
+                            conics.data_ptr(), colors.data_ptr(), opacity.data_ptr(), self._ws.data_ptr(), ws_bytes,
+                            self._gids.data_ptr(), self._bins.data_ptr(), self._packed.data_ptr(), self.status.data_ptr(), None,
+                            self._sticky.data_ptr(), None)
+                check(L.gi2d_bin_fused_ex(C.byref(a), stream), "bin_fused_rows")
                 # H here is the padded buffer height so that every pixel row of the band exists
                 check(L.gi2d_raster_sum_fwd_packed_rows_mc(self.TX, self.TY, self.W, self.buffer.shape[0], r0, r1, self._bins.data_ptr(),
                                                            self._packed.data_ptr(), 0, 0, self.buffer.data_ptr(), self._mc, 0, 0,
                                                            stream), "rasterize_sum_forward (rows)")
-                if torch.cuda.is_current_stream_capturing() or getattr(self, "_cap_checked", False):
+                self._frames += 1
+                if torch.cuda.is_current_stream_capturing():
                     break
-                n, over = self.status.tolist()
+                if getattr(self, "_cap_checked", False) and self._frames % self.check_every:
+                    break
+                # first frames of a capacity: this frame's own status; later, every `check_every` frames: the sticky pair, which
+                # remembers an overflow of ANY frame since it was last cleared (a later frame or model may have more
+                # intersections in this band than the one the capacity was learned on)
+                n, over = (self._sticky if getattr(self, "_cap_checked", False) else self.status).tolist()
                 if not over:
                     self._cap_checked = True
                     break
+                self._sticky.zero_()
                 self._cap = int(n * 1.25) + 1024
 
     def gather(self) -> torch.Tensor:

@@ -30,7 +30,7 @@ extern "C" {
 typedef struct CUstream_st *cudaStream_t;
 #endif
 
-#define GI2D_ABI_VERSION 1
+#define GI2D_ABI_VERSION 2
 #define GI2D_ERR_INVALID 1
 #define GI2D_ERR_WORKSPACE 2
 #define GI2D_ERR_CUDA_BASE 1000
@@ -67,6 +67,16 @@ int gi2d_decode_project_cholesky_fwd(int N, const void *xyz_half, const void *co
 int gi2d_project_scale_rot_fwd(int N, const float *means2d, const float *scales2d, const float *rotation, int H, int W,
                                int TX, int TY, float *xys, float *depths, int *radii, float *conics,
                                int *num_tiles_hit, cudaStream_t stream);
+
+/* Either projection (mode 0: p_a = L (N,3), p_b unused; mode 1: p_a = scales2d (N,2), p_b = rotation (N,1)) that ALSO
+ * publishes sum(num_tiles_hit) -- the number compute_cumulative_intersects reads back with `.item()`
+ * (gsplat/gsplat/utils.py:116-118, quirk Q12) -- as a by-product of the kernel: to *total_dev (device) and / or to
+ * *total_host, MAPPED PINNED HOST memory that the caller presets to a negative value and polls.  By the time the caller
+ * enters rasterize_gaussians_sum the word has normally arrived, so the binning workspace can be sized exactly without a
+ * stream synchronisation and without an overflow / retry protocol.  Either pointer may be NULL. */
+int gi2d_project_fwd_total(int mode, int N, const float *means2d, const float *p_a, const float *p_b, int H, int W, int TX, int TY,
+                           float *xys, float *depths, int *radii, float *conics, int *num_tiles_hit, int *total_dev,
+                           int *total_host, cudaStream_t stream);
 
 /* Replaces project_gaussians_2d_backward (ext.cpp:17 -> bindings.cu:902-949 -> backward2d.cu:8-51), including the
  * reference's doubled off-diagonal term (Q5).  v_cov2d (N,3) may be NULL (the Python layer discards it).
@@ -162,6 +172,29 @@ int gi2d_bin_fused_rows_notify(int N, int TX, int TY, int ty_begin, int ty_end, 
                                int capacity, void *ws, size_t ws_bytes, int *gids_sorted, int *tile_bins, float *packed,
                                int *status_out, int *status_host, cudaStream_t stream);
 
+/* gi2d_bin_fused_rows_notify with optional extras, as one argument block:
+ *   status_sticky (2 int32, device, may be NULL): [0] = max over all launches of n_isect (atomicMax), [1] |= overflow.
+ *     Only the host clears it -- a caller replaying a captured graph polls it now and then instead of after every launch.
+ *   zero_grads12 ((N,12) fp32, 16-byte aligned, may be NULL): zero-filled by the chain (it walks every Gaussian anyway):
+ *     the gradient rows gi2d_raster_sum_bwd_packed_acc accumulates into, without a memset in front of the backward pass. */
+typedef struct gi2d_bin_args {
+    int N, TX, TY, ty_begin, ty_end, capacity;
+    const float *xys;
+    const int *radii, *num_tiles_hit;
+    const float *conics, *colors, *opacities;
+    void *ws;
+    size_t ws_bytes;
+    int *gids_sorted, *tile_bins;
+    float *packed;
+    int *status_out, *status_host, *status_sticky;
+    float *zero_grads12;
+} gi2d_bin_args;
+int gi2d_bin_fused_ex(const gi2d_bin_args *args, cudaStream_t stream);
+/* gi2d_repack_records that also zero-fills zero_grads12 ((N,12), may be NULL) like gi2d_bin_fused_ex does. */
+int gi2d_repack_records_ex(int capacity, const int *gids_sorted, const int *status, const float *xys, const float *conics,
+                           const float *colors, const float *opacities, float *packed, int N, float *zero_grads12,
+                           cudaStream_t stream);
+
 /* ---- accumulated-sum rasterizer --------------------------------------------------------------------------------- */
 
 /* Replaces rasterize_sum_forward (ext.cpp:22 -> bindings.cu:400-469 -> forward.cu:512-627).
@@ -205,6 +238,11 @@ int gi2d_raster_sum_bwd(int N, int TX, int TY, int W, int H, const int *gids_sor
  * 48-byte row per Gaussian: {v_xy.x, v_xy.y, v_conic.x, v_conic.y | v_conic.z, v_colors.rgb | v_opacity, 0, 0, 0}. */
 int gi2d_raster_sum_bwd_packed(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
                                const float *v_out, float *grads12, cudaStream_t stream);
+
+/* Same WITHOUT the zero fill (grads12 was zeroed by gi2d_bin_fused_ex / gi2d_repack_records_ex); v_scale: optional DEVICE
+ * scalar multiplied into v_out (NULL = 1). */
+int gi2d_raster_sum_bwd_packed_acc(int N, int TX, int TY, int W, int H, const int *tile_bins, const float *packed,
+                                   const float *v_out, const float *v_scale, float *grads12, cudaStream_t stream);
 
 /* ---- loss epilogue --------------------------------------------------------------------------------- */
 

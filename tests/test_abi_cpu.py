@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     missing = [n for n in declared() if not hasattr(lib, n)]
     assert not missing, f"declared in include/gi2d.h but not exported by libgi2d.so: {missing}"
     assert set(_lib.EXPORTS) == set(declared()), "gaussianimage_b200/_lib.py signatures out of sync with include/gi2d.h"
-    assert _lib.lib().gi2d_abi_version() == 1
+    assert _lib.lib().gi2d_abi_version() == 2
     assert _lib.lib().gi2d_status_string(0) == b"ok" and _lib.lib().gi2d_status_string(2) == b"workspace too small"
 
 
@@ -60,8 +60,9 @@ def test_host_glue_loads_binds_the_same_library_and_checks_inputs():
     from gaussianimage_b200 import _lib
     _lib.build_glue()
     T = _lib.glue()
-    assert T is not None and T.abi_version() == 1
-    for name in ("project_fwd", "project_bwd_packed", "fused_forward", "raster_bwd_packed"):
+    assert T is not None and T.abi_version() == 2
+    for name in ("project_fwd", "project_bwd_packed", "fused_forward", "raster_bwd_packed", "project_autograd", "rasterize",
+                 "check_overflow", "get_capacity", "set_capacity", "stats"):
         assert callable(getattr(T, name))
     mapped = {line.split()[-1] for line in open("/proc/self/maps") if "libgi2d" in line}
     assert mapped == {str(_lib.LIB_PATH)}, mapped          # one copy of the product library (it owns device-side state)
@@ -72,13 +73,19 @@ def test_host_glue_loads_binds_the_same_library_and_checks_inputs():
 
 
 def test_cpp_autograd_switch_routes_the_operators_and_still_refuses_cpu_tensors():
-    """GI2D_CPP_AUTOGRAD / set_cpp_autograd: the operators as C++ autograd Functions (opt-in).  No compute without a GPU:
-    the route must be taken (the error comes from the C++ input check) and must fail as loudly as the Python one."""
+    """GI2D_CPP_AUTOGRAD / set_cpp_autograd: the operators as C++ autograd Functions (the default when the glue is built) or as
+    Python ones.  No compute without a GPU: either route must be taken and must fail loudly on CPU tensors."""
     import torch
     import gaussianimage_b200 as G
     from gaussianimage_b200 import _lib
     _lib.build_glue()
-    assert _lib.cpp_autograd() is None or _lib._cpp_autograd          # off unless the environment asked for it
+    import os
+    assert _lib._cpp_autograd == (os.environ.get("GI2D_CPP_AUTOGRAD", "1") != "0")
+    prev = _lib._cpp_autograd
+    _lib.set_cpp_autograd(False)
+    assert _lib.cpp_autograd() is None
+    with pytest.raises(RuntimeError, match="means2d must be a CUDA tensor"):
+        G.project_gaussians_2d(torch.zeros(4, 2), torch.ones(4, 3), 32, 32, (2, 2, 1))
     _lib.set_cpp_autograd(True)
     try:
         assert _lib.cpp_autograd() is _lib.glue()
@@ -86,5 +93,13 @@ def test_cpp_autograd_switch_routes_the_operators_and_still_refuses_cpu_tensors(
             G.project_gaussians_2d(torch.zeros(4, 2), torch.ones(4, 3), 32, 32, (2, 2, 1))
         with pytest.raises(RuntimeError, match="means2d must be a CUDA tensor"):
             G.project_gaussians_2d_scale_rot(torch.zeros(4, 2), torch.ones(4, 2), torch.ones(4, 1), 32, 32, (2, 2, 1))
+        # CPU tensors never reach the fused chain: rasterize() declines (not the output of one of our projections), the staged
+        # sequence then refuses the CPU tensor
+        z = torch.zeros(4, 2)
+        assert _lib.glue().rasterize(z, torch.zeros(4), torch.zeros(4, dtype=torch.int32), torch.zeros(4, 3), torch.zeros(4, dtype=torch.int32),
+                                     torch.zeros(4, 3), torch.ones(4, 1), torch.ones(3), 32, 32, False) == []
+        with pytest.raises(RuntimeError, match="must be a CUDA tensor"):
+            G.rasterize_gaussians_sum(z, torch.zeros(4), torch.zeros(4, dtype=torch.int32), torch.zeros(4, 3), torch.zeros(4, dtype=torch.int32),
+                                      torch.zeros(4, 3), torch.ones(4, 1), 32, 32)
     finally:
-        _lib.set_cpp_autograd(False)
+        _lib.set_cpp_autograd(prev)

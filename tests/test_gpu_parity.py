@@ -542,15 +542,38 @@ def test_fused_chain_reports_overflow_and_does_not_write_out_of_bounds():
     torch.cuda.synchronize()
     assert status.tolist() == [n_true, 1]
     assert (gids[cap:] == -7).all() and (packed[cap * 12:] == -7.0).all()
-    # the operator recovers by itself: strict mode grows the capacity and redoes the pass
+    # the operator itself cannot be made to truncate in strict mode, whatever capacity an earlier phase has learned: the C++
+    # operators size the workspace from the projection's intersection total, the Python Functions grow it and redo the pass
     from gaussianimage_b200 import rasterize_sum as RS
-    RS._capacity[(torch.device(DEV).index, N, TX, TY)] = cap
+    idx = torch.device(DEV).index
+    RS.set_capacity(idx, N, TX, TY, cap)
     out = G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, d.colors, d.opacity, s.H, s.W)
     want, _ = oracle_chain(s)
     amb = O.rasterize_sum_forward(s.H, s.W, _["gaussian_ids_sorted"], _["tile_bins"], _["xys"], _["conics"], _np(s.colors),
                                   _np(s.opacity), want_ambig=True)[3].astype(bool)
     assert_image_close(_np(out), want, "image after overflow retry", exclude=amb)
-    assert RS._capacity[(torch.device(DEV).index, N, TX, TY)] > n_true
+    assert RS.get_capacity(idx, N, TX, TY) > n_true
+    assert G.check_overflow(DEV) == n_true
+    # sync-free mode (what a captured graph runs): the truncation is REPORTED -- by the sticky status, however many launches
+    # later it is read -- the capacity is raised, the memoised binning dropped, and re-running the step is then correct
+    G.set_sync_free(True)
+    try:
+        RS.set_capacity(idx, N, TX, TY, cap)
+        G.set_memoise_binning(True)                                     # (also clears the memo)
+        pr = G.project_gaussians_2d(d.means2d, d.cholesky, s.H, s.W, s.tile_bounds)
+        G.rasterize_gaussians_sum(*pr, d.colors, d.opacity, s.H, s.W)     # truncated, silently
+        for _k in range(3):                                             # later launches that fit must not hide it
+            small = make_scene(s.H, s.W, 64, seed=3).to(DEV)
+            pr2 = G.project_gaussians_2d(small.means2d, small.cholesky, s.H, s.W, s.tile_bounds)
+            G.rasterize_gaussians_sum(*pr2, small.colors, small.opacity, s.H, s.W)
+        with pytest.raises(RuntimeError, match="exceeded the workspace capacity"):
+            G.check_overflow(DEV)
+        assert RS.get_capacity(idx, N, TX, TY) > n_true
+        out2 = G.rasterize_gaussians_sum(*pr, d.colors, d.opacity, s.H, s.W)   # same projection: must NOT re-use truncated lists
+        assert_image_close(_np(out2), want, "image after sync-free overflow recovery", exclude=amb)
+        G.check_overflow(DEV)
+    finally:
+        G.set_sync_free(False)
 
 
 # ------------------------------------------------------------------------------- memoised binning (Q13)
@@ -578,9 +601,9 @@ def test_three_renders_of_one_projection_reuse_the_binning_bit_for_bit(name, syn
         _, w_out, w_gauss, w_alpha = _model_forward(d, s, colors, opac)
         w_grads = torch.autograd.grad((w_out * d.gt).sum() + (w_alpha ** 2).sum(), [colors, opac])
         G.set_memoise_binning(True)
-        h0 = RS.geometry_hits
+        h0 = RS.stats()["geometry_hits"]
         pr, out, gauss, alpha = _model_forward(d, s, colors, opac)
-        assert RS.geometry_hits == h0 + 2
+        assert RS.stats()["geometry_hits"] == h0 + 2
         grads = torch.autograd.grad((out * d.gt).sum() + (alpha ** 2).sum(), [colors, opac])   # backward THROUGH a re-used list
         for got, want in ((out, w_out), (gauss, w_gauss), (alpha, w_alpha)):
             assert torch.equal(got, want)
@@ -591,10 +614,10 @@ def test_three_renders_of_one_projection_reuse_the_binning_bit_for_bit(name, syn
                                        want_all=True)
         assert_image_close(_np(alpha), o_alpha, "alpha map vs oracle")
         # an in-place change of the geometry invalidates the entry (version counter), a new projection too
-        h1 = RS.geometry_hits
+        h1 = RS.stats()["geometry_hits"]
         pr[0].add_(0.25)
         moved = G.rasterize_gaussians_sum(*pr, colors, opac, s.H, s.W)
-        assert RS.geometry_hits == h1
+        assert RS.stats()["geometry_hits"] == h1
         G.set_memoise_binning(False)
         w_moved = G.rasterize_gaussians_sum(*pr, colors, opac, s.H, s.W)
         assert torch.equal(moved, w_moved)
@@ -618,10 +641,10 @@ def test_model_forward_under_graph_capture_reuses_the_binning():
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
-        h0 = RS.geometry_hits
+        h0 = RS.stats()["geometry_hits"]
         with torch.cuda.graph(g):
             _, out, gauss, alpha = _model_forward(d, s, colors, opac)
-        assert RS.geometry_hits == h0 + 2
+        assert RS.stats()["geometry_hits"] == h0 + 2
         for _ in range(3):
             g.replay()
         torch.cuda.synchronize()
