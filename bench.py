@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--workload", default="fit", choices=["fit", "render", "decode8k", "kodak"])
     ap.add_argument("--config", default=None, help="C1|C2|C3|C5 (default: C2 for fit/render, C5 for decode8k)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the render / Kodak / decode8k / reference-CUDA legs of the default run")
     return ap.parse_args()
 
 
@@ -93,6 +94,17 @@ def measured_peaks():
     if p.exists():
         return json.loads(p.read_text()), "measured"
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+def workload_string(name, param, workload, W, H, N):
+    """config.workload -- the SAME string in both arms (the driver compares them)."""
+    what = {"fit": "fit fwd+bwd", "render": "render", "decode8k": "render-only decode", "kodak": "24 independent fits"}[workload]
+    return f"{name}: {param} {what}, {W}x{H}, {N} Gaussians"
+
+
+def spread(ts_ms):
+    """min / median / max of the K per-step CUDA-event times, in ms."""
+    return {"min": min(ts_ms), "median": statistics.median(ts_ms), "max": max(ts_ms)}
 
 
 def workload_config(args):
@@ -158,7 +170,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{name}: {param} {args.workload}, {W}x{H}, {N} Gaussians", "host_threads": cores},
+            "config": {"workload": workload_string(name, param, args.workload, W, H, N), "host_threads": cores},
             "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port",
                              "sample": f"{steps} full {args.workload} steps of {name} (oracle/gi2d_oracle.c, OpenMP)"},
             "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -269,6 +281,43 @@ def count_evals(tile_bins, H, W):
     return int((cnt * ph * pw).sum())
 
 
+def count_executed(packed, tile_bins, H, W):
+    """Pixel-Gaussian pairs the rasterizers really evaluate: both cull every record to its visible rectangle
+    (csrc/raster.cu: record_rect, from the extents carried in the packed record) and evaluate the ALIGNED 4x2 PIXEL BLOCKS
+    that rectangle touches -- 8 pixel slots per block.  Deterministic from the records; torch restatement of record_rect."""
+    import torch
+    TX, TY = (W + 15) // 16, (H + 15) // 16
+    bins = tile_bins.to(torch.int64)
+    cnt = (bins[:, 1] - bins[:, 0]).clamp(0, 256)                          # Q1: only the first 256 of a tile are staged
+    T = TX * TY
+    tile = torch.repeat_interleave(torch.arange(T, device=bins.device), cnt[:T])
+    first = torch.repeat_interleave(bins[:T, 0], cnt[:T])
+    rank = torch.arange(tile.numel(), device=bins.device) - torch.repeat_interleave(torch.cumsum(cnt[:T], 0) - cnt[:T], cnt[:T])
+    rec = packed.view(-1, 12)[first + rank]
+    x, y, ex, ey = rec[:, 0], rec[:, 1], rec[:, 10], rec[:, 11]
+    tx0, ty0 = ((tile % TX) * 16).float(), ((tile // TX) * 16).float()
+    fx0, fx1 = torch.ceil(x - ex) - tx0, torch.floor(x + ex) - tx0
+    fy0, fy1 = torch.ceil(y - ey) - ty0, torch.floor(y + ey) - ty0
+    vis = (ex >= 0) & (fx0 <= fx1) & (fy0 <= fy1) & (fx1 >= 0) & (fy1 >= 0) & (fx0 <= 15) & (fy0 <= 15)
+    whole = torch.isinf(ex)                                                # no bound available: the whole tile
+    lx0, lx1 = fx0.clamp(0, 15).nan_to_num(0).long(), fx1.clamp(0, 15).nan_to_num(15).long()
+    ly0, ly1 = fy0.clamp(0, 15).nan_to_num(0).long(), fy1.clamp(0, 15).nan_to_num(15).long()
+    blocks = ((lx1 // 4) - (lx0 // 4) + 1) * ((ly1 // 2) - (ly0 // 2) + 1)
+    blocks = torch.where(whole, torch.full_like(blocks, 32), blocks) * (vis | whole)
+    return int(blocks.sum().item()) * 8
+
+
+def ncu_counters(kernel):
+    """Hardware counters of the committed `ncu --set full` capture of this kernel at C2 (profiles/ncu_counters.json, written
+    by tools/ncu_summary.py from the capture of tools/gpu/r2_ncu_raster.sh) -- NOT measured in this run (a bench value is
+    never taken under a profiler); they say what the roofline fraction cannot: which pipe is busy and how full the SMs are."""
+    p = ROOT / "profiles" / "ncu_counters.json"
+    if not p.exists():
+        return None
+    d = json.loads(p.read_text())
+    return d.get(kernel) or d.get({"binning_chain": "bin_small"}.get(kernel, kernel))
+
+
 def kernel_rooflines(step, flush, reps, peaks, sm_mhz):
     """Time the individual C-ABI stages alone (CUDA events, L2 flushed) and relate them to their rooflines."""
     import torch
@@ -291,13 +340,14 @@ def kernel_rooflines(step, flush, reps, peaks, sm_mhz):
         r = fused_chain(xys, radii, conics, nth, colors, opac, step.bg, H, W, cap)
         n_isect = int(r["status"][0].item())
         E = count_evals(r["tile_bins"], H, W)
+        E_eval = count_executed(r["packed"], r["tile_bins"], H, W)
         v_out = torch.randn(H, W, 3, device=dev) * 1e-3
-        grads = torch.empty(N, 12, device=dev)
+        grads = torch.zeros(N, 12, device=dev)
         v_xy, v_conic = grads[:, 0:2].contiguous(), grads[:, 2:5].contiguous()
 
-        def bwd():
-            check(L.gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, r["tile_bins"].data_ptr(), r["packed"].data_ptr(), v_out.data_ptr(),
-                                               grads.data_ptr(), st), "bwd")
+        def bwd():          # the kernel ALONE: the zero fill of the gradient rows belongs to the binning chain (gi2d_bin_fused_ex)
+            check(L.gi2d_raster_sum_bwd_packed_acc(N, TX, TY, W, H, r["tile_bins"].data_ptr(), r["packed"].data_ptr(), v_out.data_ptr(),
+                                                   0, grads.data_ptr(), st), "bwd")
         out2 = torch.empty(H, W, 3, device=dev)
 
         def fwd():
@@ -328,9 +378,9 @@ def kernel_rooflines(step, flush, reps, peaks, sm_mhz):
     P = max(1, ((max(T, 2) - 1).bit_length() + 7) // 8)
     fp32_peak = 148 * 128 * 2 * (sm_mhz or peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e12
     hbm = peaks["hbm_gbs"]
-    alg = {   # algorithmic work per launch, SURVEY.md section 8d
-        "raster_bwd": ("fp32", 54.0 * E / 1e12, "TFLOP/s", fp32_peak),
-        "raster_fwd": ("fp32", 22.0 * E / 1e12, "TFLOP/s", fp32_peak),
+    alg = {   # work per launch: SURVEY.md section 8d's per-pair figure x the pairs the kernel EXECUTES (E_eval; E = all pairs)
+        "raster_bwd": ("fp32", 54.0 * E_eval / 1e12, "TFLOP/s", fp32_peak),
+        "raster_fwd": ("fp32", 22.0 * E_eval / 1e12, "TFLOP/s", fp32_peak),
         "binning_chain": ("hbm", (20.0 * N + n_isect * (12 + 16 * P) + 8 * T + 48.0 * n_isect) / 1e9, "GB/s", hbm),
         "project_fwd": ("hbm", 52.0 * N / 1e9, "GB/s", hbm),
         "project_bwd": ("hbm", 68.0 * N / 1e9, "GB/s", hbm),
@@ -339,7 +389,92 @@ def kernel_rooflines(step, flush, reps, peaks, sm_mhz):
     for k, (bound, work, unit, peak) in alg.items():
         ach = work / res[k]
         table[k] = {"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "us": res[k] * 1e6}
-    return table, dict(n_isect=n_isect, E=E, N=N)
+        if bound == "fp32":     # the survey's figure over ALL pairs of the tiles (what the reference evaluates): a work ratio, not a utilisation
+            per_pair = 54.0 if k == "raster_bwd" else 22.0
+            table[k]["frac_algorithmic"] = per_pair * E / 1e12 / res[k] / peak
+            table[k]["flops_executed"] = per_pair * E_eval
+            table[k]["flops_algorithmic"] = per_pair * E
+    return table, dict(n_isect=n_isect, E=E, E_eval=E_eval, N=N)
+
+
+
+def measure_render(d, scene_cpu, param, flush, K, Wm):
+    """BASELINE metric, first third: render FPS (train.py:242-249 -- the mean of repeated model() calls under no_grad) on the
+    same scene: CUDA-graph replay (events, L2 flushed) and the eager strict public API (wall clock, what an unchanged caller gets)."""
+    import torch
+    st = FitStep(d, scene_cpu, param)
+    st.capture(render_only=True)
+    for _ in range(Wm):
+        st.graph.replay()
+    torch.cuda.synchronize()
+    ts = timed_replays(st.graph.replay, K, flush)
+    with torch.no_grad():
+        for _ in range(5):
+            st.forward()
+        torch.cuda.synchronize()
+        n = max(K, 50)
+        t0 = time.perf_counter()
+        for _ in range(n):
+            st.forward()
+        torch.cuda.synchronize()
+        eager = n / (time.perf_counter() - t0)
+    return {"render_fps": 1e3 * K / sum(ts), "render_ms_per_frame": sum(ts) / K, "render_ms_spread": spread(ts),
+            "render_fps_eager_strict": eager, "timing": "graph replay: CUDA events, L2 flushed between frames; eager: wall clock, back to back"}
+
+
+def measure_kodak_quick(rank, world, dev, K, Wm):
+    """BASELINE metric, last third, with few timed iterations: every rank fits ONE Kodak-sized image (whole training iteration
+    incl. Adan as one CUDA graph, gaussianimage_b200/fit.py) for K iterations; imgs/s at the reference's 50 000 iterations per
+    image, aggregated over the ranks (max-over-ranks time).  `--workload kodak` is the full 24-image form."""
+    import torch
+    import torch.distributed as dist
+    from gaussianimage_b200.fit import GraphFitter
+    from gaussianimage_b200.synth import make_scene
+    H, W, N, REF_ITERS = 512, 768, 70_000, 50_000
+    gt = make_scene(H, W, 1, seed=100 + rank).gt.permute(2, 0, 1).unsqueeze(0).contiguous().to(dev)
+    f = GraphFitter(gt, N, lr=0.018, seed=rank + 1)
+    f.capture()
+    f.run(Wm)
+    p0 = f.psnr()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    f.run(K)
+    b.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    its = world * K / (t.item() / 1e3)
+    return {"kodak_imgs_per_s": its / REF_ITERS, "training_iterations_per_s": its, "us_per_training_iteration": 1e3 * t.item() / K,
+            "psnr_db_rank0": [p0, f.psnr()], "graph_recaptures": f.recaptures,
+            "note": f"{world} image(s) in parallel, {K} timed iterations each, extrapolated to {REF_ITERS} iterations per image"}
+
+
+def reference_cuda_leg(name, reps=100):
+    """The north_star target beside the line: the REFERENCE's own CUDA kernels (oracle/_ref, compiled from /root/reference
+    where it exists and shipped with the repository snapshot) around the reference's own Python staging, timed by
+    tests/bench_vs_refcuda.py in a SUBPROCESS (this process never loads reference code)."""
+    ref = ROOT / "oracle" / "_ref"
+    if not any(ref.glob("libgsplat_ref_*.so")):
+        return {"unavailable": "oracle/_ref/libgsplat_ref_*.so not built on this machine"}
+    out = ROOT / "gpurun_out" / f"_bench_vs_refcuda_{name}.json"
+    try:
+        out.parent.mkdir(exist_ok=True)
+        r = subprocess.run([sys.executable, str(ROOT / "tests" / "bench_vs_refcuda.py"), "--config", name, "--reps", str(reps), "--out", str(out)],
+                           capture_output=True, text=True, timeout=240)
+        if r.returncode != 0:
+            return {"unavailable": "tests/bench_vs_refcuda.py failed: " + r.stderr[-300:]}
+        d = json.loads(out.read_text())
+        ref_arm = d.get("reference_cuda_fast") or d.get("reference_cuda_jit")
+        return {"fit_iters_per_s": ref_arm["fit_iters_per_s"], "render_fps": ref_arm["render_fps"],
+                "model_forward_per_s": ref_arm["model_forward_per_s"], "flags": ref_arm["flags"],
+                "jit_build": d.get("reference_cuda_jit"), "ours_same_harness": d.get("gi2d_b200"),
+                "speedup_vs_reference_cuda": d.get("speedup_vs_reference_cuda"), "timing": d.get("timing")}
+    except Exception as e:                                  # noqa: BLE001  (a side leg must not cost the bench line)
+        return {"unavailable": f"{type(e).__name__}: {e}"}
 
 
 def run_b200(args):
@@ -616,10 +751,37 @@ def run_b200(args):
             loss.item()
         e2e["eager_strict_iters_per_s"] = min(K, 50) / (time.perf_counter() - t0)
 
+    # ---- the rest of BASELINE.json's metric at this N (render FPS, Kodak imgs/s) and the sharded config (8K decode, strong
+    # scaling over the ranks): every rank takes part, rank 0 reports them under `extras`
+    more = {}
+    if args.workload == "fit" and name == "C2" and not args.no_extras:
+        Kx = min(K, 50)
+        try:
+            more.update(measure_render(d, scene_cpu, param, flush, Kx, Wm))
+        except Exception as e:                              # noqa: BLE001
+            more["render_error"] = f"{type(e).__name__}: {e}"
+        barrier()
+        try:
+            more.update(measure_kodak_quick(rank, world, dev, max(Kx, 100), Wm))
+        except Exception as e:                              # noqa: BLE001
+            more["kodak_error"] = f"{type(e).__name__}: {e}"
+        barrier()
+        del flush                                           # 256 MiB back before the 8K frame buffers are allocated
+        torch.cuda.empty_cache()
+        try:
+            line8k = measure_decode8k(args, rank, world, dev, min(K, 20), Wm, with_e2e=False)
+            if line8k is not None:
+                more["decode8k"] = dict(line8k["summary"], clocks=line8k["clocks"], n_gpus=world, scaling="strong")
+        except Exception as e:                              # noqa: BLE001
+            more["decode8k"] = {"error": f"{type(e).__name__}: {e}"}
+        barrier()
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    if world > 1:
+        dist.destroy_process_group()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
         return
+    if more and not args.no_extras:
+        more["reference_cuda"] = reference_cuda_leg(name)
 
     # ---- roofline of the individual kernels (rank 0, timed alone) -----------------------------------------------
     with ClockSampler(local) as clk2:
@@ -628,6 +790,7 @@ def run_b200(args):
     fp32_peak = 148 * 128 * 2 * (k_mhz or 1965.0) * 1e6 / 1e12
     for v in table.values():
         if v["bound"] == "fp32":
+            v["frac_algorithmic"] *= v["peak"] / fp32_peak
             v["peak"], v["frac"] = fp32_peak, v["achieved"] / fp32_peak
     dom = "raster_fwd" if render_only else "raster_bwd"
     roof = dict(table[dom])
@@ -635,9 +798,15 @@ def run_b200(args):
     tp = ROOT / "profiles" / "ncu_traffic.json"           # dram__bytes_read+write per launch from the ncu --set full capture (C2)
     if tp.exists() and name == "C2":
         traffic = json.loads(tp.read_text()).get(dom, {}).get("dram_bytes")
+    hw = ncu_counters(dom) if name == "C2" else None
     roof.update({"kernel": dom, "traffic": traffic, "peak_source": f"148 SMs x 128 FP32 lanes x 2 x {k_mhz} MHz observed while timing "
                  "(FP32 pipe; the contract's hbm/tensor bounds do not apply to this kernel, see DESIGN.md section 5)",
-                 "algorithmic_flops_per_launch": (22.0 if render_only else 54.0) * counts["E"]})
+                 "frac_executed": roof["frac"],
+                 "note": "achieved / frac = executed work: 22 (fwd) / 54 (bwd) FLOP per evaluated pixel-Gaussian pair (SURVEY 8d) x the pairs "
+                         "the kernel evaluates after culling (config.pair_evaluations_executed) / the kernel's own CUDA-event time; "
+                         "frac_algorithmic counts every pair of the tiles, which the reference evaluates and this kernel provably "
+                         "need not -- it is a work ratio and may exceed 1",
+                 "launch_us": roof["us"], "ncu": hw})
 
     cpu = cpu_torch = None
     if not args.no_cpu_baseline and world == 1:
@@ -666,32 +835,43 @@ def run_b200(args):
         "value": world * K / (total_ms / 1e3), "unit": "frames/s" if render_only else UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"{name}: {param} {'render' if render_only else 'fit fwd+bwd'}, {W}x{H}, {N} Gaussians, "
-                               f"{counts['n_isect']} tile intersections, E={counts['E']} pixel-Gaussian evaluations",
+        "config": {"workload": workload_string(name, param, args.workload, W, H, N),
+                   "tile_intersections": counts["n_isect"], "pair_evaluations_algorithmic": counts["E"],
+                   "pair_evaluations_executed": counts["E_eval"],
                    "l2": "256 MiB buffer rewritten between timed steps (flush)", "parallelism": f"image-parallel x{world}, no collective",
                    "peaks": peaks_src},
+        "ms_per_step_spread": spread(ts),
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
         "roofline": roof, "stages": table, "cpu_baseline": cpu, "cpu_baseline_torch": cpu_torch,
         "extras": {"warm_l2_back_to_back_ms_per_step": warm_ms, "warm_l2_iters_per_s": 1e3 / warm_ms,
                    "n_isect_checked": n_isect,
-                   "fused_loss_epilogue_ms_per_step": fused_ms, "fused_loss_epilogue_iters_per_s": (1e3 / fused_ms) if fused_ms else None},
+                   "fused_loss_epilogue_ms_per_step": fused_ms, "fused_loss_epilogue_iters_per_s": (1e3 / fused_ms) if fused_ms else None,
+                   **more},
     }
     print(json.dumps(line), flush=True)
+
+
+def run_decode8k(args, rank, world, dev):
+    import torch.distributed as dist
+    line = measure_decode8k(args, rank, world, dev, args.steps, max(args.warmup, 3))
+    if rank == 0:
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_decode8k(args, rank, world, dev):
+def measure_decode8k(args, rank, world, dev, K, Wm, with_e2e=True):
     """BASELINE config 5: render-only codec decode (test_quantize.py:66-90 -> decompress_wo_ec), 7680x4320, 1M Gaussians,
-    tile rows sharded over the ranks, one in-place NCCL all-gather of the frame."""
+    tile rows sharded over the ranks, the frame completed on every rank (all-gather fused into the rasterizer through NVLS
+    multicast stores, or one in-place NCCL all-gather).  Collective: every rank must call it; rank 0 gets the line."""
     import torch
     import torch.distributed as dist
     from gaussianimage_b200.sharded import RowShardedRenderer
     from gaussianimage_b200._lib import lib as _gi2d_lib
-    from gaussianimage_b200.synth import make_scene
+    from gaussianimage_b200.synth import CONFIGS, make_scene
 
-    name, H, W, N, param = workload_config(args)
-    K, Wm = args.steps, max(args.warmup, 3)
+    name = "C5"
+    H, W, N, param = CONFIGS[name]
     peaks, peaks_src = measured_peaks()
     sc = make_scene(H, W, N, seed=1)                       # the same frame on every rank
     # "compressed" representation like compress_wo_ec (gaussianimage_cholesky.py:154-159): fp16 positions,
@@ -779,6 +959,7 @@ def run_decode8k(args, rank, world, dev):
         # e2e: compressed parameters from pinned host memory every frame, a scalar checksum of the frame back.  Two frames
         # in flight: the H2D copy of frame i+1 runs on a copy stream into the other input set while frame i decodes, and the
         # host reads frame i's checksum while frame i+1 is in flight.
+        e2e_s = None
         cur = torch.cuda.current_stream()
         copy_stream = torch.cuda.Stream()
         sets = [d_in, [t.clone() for t in d_in]]
@@ -805,22 +986,22 @@ def run_decode8k(args, rank, world, dev):
                     ev_done[(i - 1) & 1].synchronize()          # host consumes frame i-1 while frame i is in flight
                     float(res[(i - 1) & 1][0])
             ev_done[(n - 1) & 1].synchronize()
-        for e in ev_done:
-            e.record(cur)
-        e2e_run(4)
-        barrier()
-        t0 = time.perf_counter()
-        e2e_run(K)
-        torch.cuda.synchronize()
-        e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-        e2e_s = e2e_s.item()
+        if with_e2e:
+            for e in ev_done:
+                e.record(cur)
+            e2e_run(4)
+            barrier()
+            t0 = time.perf_counter()
+            e2e_run(K)
+            torch.cuda.synchronize()
+            e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+            e2e_s = e2e_s.item()
     n_band = int(R.status[0].item()) if R.status is not None else 0
+    del R, R_nccl
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return None
     frame_bytes = H * W * 12
     fused_ms = total_ms / K
     if nccl_ms is not None and nccl_ms < fused_ms:      # both exchange methods were timed with the same protocol: quote the faster
@@ -831,8 +1012,8 @@ def run_decode8k(args, rank, world, dev):
         "metric": "sharded decode FPS @7680x4320, 1M Gaussians", "value": K / (total_ms / 1e3), "unit": "frames/s", "n_gpus": world,
         "steps": K, "warmup": Wm, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{name}: render-only decode, {W}x{H}, {N} Gaussians, tile rows sharded x{world}, "
-                               f"{n_band} tile intersections on rank 0", "l2": "256 MiB buffer rewritten between timed steps (flush)",
+        "config": {"workload": workload_string(name, param, "decode8k", W, H, N), "tile_rows_sharded_over": world,
+                   "tile_intersections_rank0": n_band, "l2": "256 MiB buffer rewritten between timed steps (flush)",
                    "parallelism": f"tile-row bands x{world}; {frame_bytes / 1e6:.0f} MB frame completed on every rank by: {fused_note}",
                    "nccl_allgather_ms_per_step": nccl_ms, "fused_multicast_ms_per_step": fused_ms if world > 1 else None,
                    "bands_only_ms_per_step": band_ms,      # no exchange: each rank keeps its band of the frame
@@ -840,7 +1021,7 @@ def run_decode8k(args, rank, world, dev):
                                "projection kernel; checked bit-identical to the torch-op prologue before timing",
                    "peaks": peaks_src},
         "clocks": clk.summary(),
-        "e2e": {"value": K / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in host),
+        "e2e": {"value": (K / e2e_s) if e2e_s else None, "unit": "frames/s", "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in host),
                 "d2h_bytes_per_step": 4, "mode": "compressed parameters (fp16 positions, uint8 Cholesky codes, int32 codebook indices) H2D from pinned memory every frame on a copy stream, double-buffered; frame checksum D2H and host read every frame; two frames in flight"},
         "gpu_launches": (2 + _gi2d_lib().gi2d_bin_fused_kernel_count(N, (W + 15) // 16, (H + 15) // 16)) * K,   # decode+project, binning chain, rasterizer
         "roofline": {"bound": "hbm", "achieved": (frame_bytes / world * (2 if world > 1 else 1)) / 1e9 / (total_ms / K / 1e3),
@@ -849,9 +1030,11 @@ def run_decode8k(args, rank, world, dev):
         "cpu_baseline": None,
     }
     line["roofline"]["frac"] = line["roofline"]["achieved"] / peaks["hbm_gbs"]
-    print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    wire_ms = (frame_bytes * (world - 1) / world) / 900e9 * 1e3 if world > 1 else 0.0      # inbound bytes per rank at 900 GB/s per direction
+    exch = (total_ms / K - band_ms) if band_ms is not None else 0.0
+    line["summary"] = {"fps": line["value"], "ms_per_step": total_ms / K, "bands_only_ms": band_ms, "exchange_ms": exch,
+                       "exchange_wire_floor_ms": wire_ms, "method": fused_note}
+    return line
 
 
 def run_kodak(args, rank, world, dev):

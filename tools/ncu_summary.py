@@ -17,6 +17,7 @@ KEYS = [("gpu__time_duration.sum", "us"), ("dram__bytes_read.sum", "dram rd"), (
         ("launch__registers_per_thread", "regs"), ("smsp__inst_executed.sum", "warp insts")]
 UNIT = {"Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Gbyte": 1e9}
 traffic = {}
+counters = {}
 print("| kernel | " + " | ".join(k for _, k in KEYS) + " | top stalls (pc samples) |")
 print("|---|" + "---|" * (len(KEYS) + 1))
 for rep in sys.argv[1:]:
@@ -51,4 +52,20 @@ for rep in sys.argv[1:]:
         traffic[short + ("@c5" if Path(rep).stem.endswith("c5") else "")] = {
             "dram_bytes": b("dram__bytes_read.sum") + b("dram__bytes_write.sum"), "us": float(r[idx["gpu__time_duration.sum"]]),
             "report": Path(rep).name}
+
+        def pct(key):
+            return float(r[idx[key]]) if key in idx and r[idx[key]] not in ("", "n/a") else None
+        counters[short + ("@c5" if Path(rep).stem.endswith("c5") else "")] = {
+            "duration_us": float(r[idx["gpu__time_duration.sum"]]),
+            "fma_pipe_pct": pct("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
+            "alu_pipe_pct": pct("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"),
+            "issue_active_pct": pct("sm__inst_issued.avg.pct_of_peak_sustained_active"),
+            "achieved_occupancy_pct": pct("sm__warps_active.avg.pct_of_peak_sustained_active"),
+            "dram_throughput_pct": pct("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+            "dram_bytes": b("dram__bytes_read.sum") + b("dram__bytes_write.sum"),
+            "warp_instructions": float(r[idx["smsp__inst_executed.sum"]]) if "smsp__inst_executed.sum" in idx else None,
+            "registers_per_thread": float(r[idx["launch__registers_per_thread"]]) if "launch__registers_per_thread" in idx else None,
+            "grid": r[idx["Grid Size"]], "top_stalls": [n for _, n in stalls],
+            "report": Path(rep).name, "how": "ncu --set full --clock-control none, one launch, L2 flushed before it (tools/prof_raster.py)"}
 Path("profiles/ncu_traffic.json").write_text(json.dumps(traffic, indent=1) + "\n")
+Path("profiles/ncu_counters.json").write_text(json.dumps(counters, indent=1) + "\n")
