@@ -890,13 +890,23 @@ def measure_decode8k(args, rank, world, dev, K, Wm, with_e2e=True):
     R_nccl = RowShardedRenderer(H, W, dev)
     fused_note = "single GPU: no exchange step"
     R = R_nccl
+    R_p2p = R_ce = None
     if world > 1 and os.environ.get("GI2D_FUSED_GATHER", "1") == "1":
         try:
             R = RowShardedRenderer(H, W, dev, fused=True)     # NVLS multicast stores from the rasterizer epilogue
-            fused_note = "all-gather fused into the rasterizer (multimem.st into symmetric memory) + 2 barriers"
+            fused_note = ("all-gather fused into the rasterizer (multimem.st into double-buffered symmetric memory), one barrier per "
+                          "frame on a side stream")
         except Exception as e:                                # no multicast on this box: keep the NCCL all-gather
             fused_note = f"NCCL all-gather (fused path unavailable: {type(e).__name__}: {e})"
             R = R_nccl
+        try:
+            R_p2p = RowShardedRenderer(H, W, dev, fused=True, exchange="p2p")     # plain peer stores from the rasterizer epilogue
+        except Exception as e:
+            print(f"bench: peer-store exchange unavailable ({type(e).__name__}: {e})", file=sys.stderr)
+        try:
+            R_ce = RowShardedRenderer(H, W, dev, fused=True, exchange="ce")       # copy engines push the band while the SMs go on
+        except Exception as e:
+            print(f"bench: copy-engine exchange unavailable ({type(e).__name__}: {e})", file=sys.stderr)
     elif world > 1:
         fused_note = "in-place NCCL all-gather"
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -929,33 +939,57 @@ def measure_decode8k(args, rank, world, dev, K, Wm, with_e2e=True):
             dist.all_reduce(same, op=dist.ReduceOp.MIN)
             if not int(same.item()):
                 raise RuntimeError("fused multicast frame differs from the NCCL all-gather frame")
-        barrier()
-        with ClockSampler(dev.index) as clk:
-            ts = timed_replays(decode, K, flush)
-            barrier()
-        total_ms = torch.tensor([sum(ts)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
-        total_ms = total_ms.item()
-        if R is not R_nccl:        # the plain NCCL variant beside it, same protocol
+        # Protocol (the same at every N): K frames back to back -- test_quantize.py:66-90 times its decode loop the same way --,
+        # one CUDA-event pair around the loop, the last frame complete on every rank before the end event; max over ranks.
+        # No L2 flush: a frame writes 398 MB and reads ~120 MB of records, several times the 126 MB L2.
+        def pipeline_ms(one_frame, finish):
             for _ in range(3):
-                decode(R_nccl)
+                one_frame()
+            finish()
             barrier()
-            t2 = torch.tensor([sum(timed_replays(lambda: decode(R_nccl), K, flush))], dtype=torch.float64, device=dev)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(K):
+                one_frame()
+            finish()
+            b.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
             barrier()
-            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-            nccl_ms = t2.item() / K
+            return t.item() / K
+
+        with ClockSampler(dev.index) as clk:
+            total_ms = K * pipeline_ms(lambda: R.render_compressed_async(d_in[0], d_in[1], scale, beta, bound, d_in[2], cb, opacity),
+                                       R.wait_frames)
+        serial_ts = timed_replays(decode, K, flush)                 # one frame at a time, L2 flushed in between (round-1 protocol)
+        serial_ms = torch.tensor([sum(serial_ts) / K], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(serial_ms, op=dist.ReduceOp.MAX)
+        serial_ms = serial_ms.item()
+        if R is not R_nccl:        # the plain NCCL variant beside it, same protocol
+            nccl_ms = pipeline_ms(lambda: decode(R_nccl), lambda: None)
+        p2p_ms = None
+        if R_p2p is not None:      # ... and the peer-store variant (checked against the NCCL-gathered frame first)
+            same = torch.tensor([int(torch.equal(decode(R_p2p).clone(), decode(R_nccl)))], device=dev)
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+            if not int(same.item()):
+                raise RuntimeError("peer-store frame differs from the NCCL all-gather frame")
+            p2p_ms = pipeline_ms(lambda: R_p2p.render_compressed_async(d_in[0], d_in[1], scale, beta, bound, d_in[2], cb, opacity),
+                                 R_p2p.wait_frames)
+        ce_ms = None
+        if R_ce is not None:
+            same = torch.tensor([int(torch.equal(decode(R_ce).clone(), decode(R_nccl)))], device=dev)
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+            if not int(same.item()):
+                raise RuntimeError("copy-engine frame differs from the NCCL all-gather frame")
+            ce_ms = pipeline_ms(lambda: R_ce.render_compressed_async(d_in[0], d_in[1], scale, beta, bound, d_in[2], cb, opacity),
+                                R_ce.wait_frames)
         band_ms = None
         if world > 1:              # the same decode without the exchange step: every rank keeps its band (informational)
-            def band_only():
-                return R_nccl.render_compressed_band(d_in[0], d_in[1], scale, beta, bound, d_in[2], cb, opacity)
-            for _ in range(3):
-                band_only()
-            barrier()
-            t3 = torch.tensor([sum(timed_replays(band_only, K, flush))], dtype=torch.float64, device=dev)
-            barrier()
-            dist.all_reduce(t3, op=dist.ReduceOp.MAX)
-            band_ms = t3.item() / K
+            band_ms = pipeline_ms(lambda: R_nccl.render_compressed_band(d_in[0], d_in[1], scale, beta, bound, d_in[2], cb, opacity),
+                                  lambda: None)
         # e2e: compressed parameters from pinned host memory every frame, a scalar checksum of the frame back.  Two frames
         # in flight: the H2D copy of frame i+1 runs on a copy stream into the other input set while frame i decodes, and the
         # host reads frame i's checksum while frame i+1 is in flight.
@@ -999,23 +1033,36 @@ def measure_decode8k(args, rank, world, dev, K, Wm, with_e2e=True):
                 dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
             e2e_s = e2e_s.item()
     n_band = int(R.status[0].item()) if R.status is not None else 0
-    del R, R_nccl
+    del R, R_nccl, R_p2p, R_ce
     if rank != 0:
         return None
     frame_bytes = H * W * 12
     fused_ms = total_ms / K
-    if nccl_ms is not None and nccl_ms < fused_ms:      # both exchange methods were timed with the same protocol: quote the faster
+    methods = {"multicast": fused_ms if world > 1 else None, "nccl": nccl_ms, "p2p": p2p_ms, "ce": ce_ms}
+    best = min((v, k) for k, v in methods.items() if v is not None)[1] if world > 1 else None
+    if best == "nccl":            # every exchange method was timed with the same protocol: quote the fastest
         total_ms = nccl_ms * K
-        fused_note = (f"in-place NCCL all-gather (faster here than the all-gather fused into the rasterizer via multimem.st, "
-                      f"{fused_ms:.3f} ms per frame)")
+        fused_note = "in-place NCCL all-gather after the band rasterizers"
+    elif best == "ce":
+        total_ms = ce_ms * K
+        fused_note = ("every rank rasterizes its band locally; the copy engines push it into the double-buffered symmetric frame buffer "
+                      "of every other rank (peer-to-peer copies on a side stream, one barrier per frame) while the SMs work on the next frame")
+    elif best == "p2p":
+        total_ms = p2p_ms * K
+        fused_note = ("all-gather fused into the rasterizer: every tile row stored to the double-buffered symmetric frame buffer of every "
+                      "rank (plain peer stores over NVLink), one barrier per frame on a side stream")
     line = {
         "metric": "sharded decode FPS @7680x4320, 1M Gaussians", "value": K / (total_ms / 1e3), "unit": "frames/s", "n_gpus": world,
         "steps": K, "warmup": Wm, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_string(name, param, "decode8k", W, H, N), "tile_rows_sharded_over": world,
-                   "tile_intersections_rank0": n_band, "l2": "256 MiB buffer rewritten between timed steps (flush)",
+                   "tile_intersections_rank0": n_band,
+                   "l2": "not flushed: every frame writes 398 MB and streams ~120 MB of records, several times the 126 MB L2",
                    "parallelism": f"tile-row bands x{world}; {frame_bytes / 1e6:.0f} MB frame completed on every rank by: {fused_note}",
+                   "timing": "K frames back to back, one CUDA-event pair around the loop, last frame complete on every rank; max over ranks",
                    "nccl_allgather_ms_per_step": nccl_ms, "fused_multicast_ms_per_step": fused_ms if world > 1 else None,
+                   "fused_peer_store_ms_per_step": p2p_ms, "copy_engine_exchange_ms_per_step": ce_ms,
+                   "one_frame_at_a_time_l2_flushed_ms_per_step": serial_ms,
                    "bands_only_ms_per_step": band_ms,      # no exchange: each rank keeps its band of the frame
                    "prologue": "de-quantisation (tanh of fp16 positions, 6-bit Cholesky codes, residual-VQ colours) fused into the "
                                "projection kernel; checked bit-identical to the torch-op prologue before timing",
@@ -1032,7 +1079,8 @@ def measure_decode8k(args, rank, world, dev, K, Wm, with_e2e=True):
     line["roofline"]["frac"] = line["roofline"]["achieved"] / peaks["hbm_gbs"]
     wire_ms = (frame_bytes * (world - 1) / world) / 900e9 * 1e3 if world > 1 else 0.0      # inbound bytes per rank at 900 GB/s per direction
     exch = (total_ms / K - band_ms) if band_ms is not None else 0.0
-    line["summary"] = {"fps": line["value"], "ms_per_step": total_ms / K, "bands_only_ms": band_ms, "exchange_ms": exch,
+    line["summary"] = {"fps": line["value"], "ms_per_step": total_ms / K, "one_frame_at_a_time_l2_flushed_ms": serial_ms,
+                       "bands_only_ms": band_ms, "exchange_ms": exch,
                        "exchange_wire_floor_ms": wire_ms, "method": fused_note}
     return line
 

@@ -52,6 +52,7 @@ _SIGNATURES = {
     "gi2d_bin_fused_rows_notify": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_raster_sum_fwd_packed_rows": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_raster_sum_fwd_packed_rows_mc": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gi2d_raster_sum_fwd_packed_rows_p2p": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp]),
     "gi2d_raster_sum_fwd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_raster_sum_fwd_packed": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_raster_sum_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -177,6 +177,13 @@ __device__ __forceinline__ void gather_chunk(float4 *rec, const GatherSrc &src, 
 // and writes the gradient of that loss w.r.t. out_img,  v_out = 2/(3HW) (image - gt) [0 <= out_img <= 1],  straight into the
 // buffer the backward rasterizer reads.  The squared error is summed per thread over the warp's tiles, reduced once per
 // CTA, and the last CTA to finish adds the per-CTA partials in index order: a deterministic loss, no atomics on floats.
+// Frame buffers of the OTHER ranks of a row-sharded render (peer-mapped device addresses, e.g. torch symmetric memory's
+// buffer_ptrs): the epilogue repeats every full-tile row store to each of them over NVLink (plain st.global.v4).
+struct PeerOut {
+    float *p[7];
+    int n;
+};
+
 struct LossArgs {
     const float *gt;          // target, (3,H,W) planes when gt_chw else (H,W,3)
     int gt_chw, clamp;
@@ -191,7 +198,9 @@ struct LossArgs {
 constexpr int FW_WARPS = 8;                       // warps per CTA = independent pipelines per CTA
 constexpr int FW_CHUNK = PIPE_CHUNK;
 constexpr int FW_THREADS = FW_WARPS * 32;
-constexpr size_t FW_SMEM = (size_t)FW_WARPS * PIPE_NST * PIPE_CHUNK * 48 + (size_t)FW_WARPS * PIPE_NST * 8;
+constexpr size_t FW_RING_BYTES = (size_t)FW_WARPS * PIPE_NST * PIPE_CHUNK * 48;
+constexpr size_t FW_OUT_BYTES = (size_t)FW_WARPS * GI2D_TILE_PIX * 3 * 4;        // one output tile per warp (epilogue staging)
+constexpr size_t FW_SMEM = FW_RING_BYTES + FW_OUT_BYTES + (size_t)FW_WARPS * PIPE_NST * 8;
 
 // SPLIT = 1: a warp renders a whole tile, a lane a 4x2 pixel block (images with many tiles: 8K decode).
 // SPLIT = 2: a warp renders HALF a tile (8 pixel rows), a lane a 2x2 block; the two halves of a tile go to different
@@ -199,12 +208,13 @@ constexpr size_t FW_SMEM = (size_t)FW_WARPS * PIPE_NST * PIPE_CHUNK * 48 + (size
 //            (768x512 has only 1536 tiles for 148 SMs), the same instruction count (finer culling pays for the second
 //            set of masks).
 template <bool TMA, bool AUX, bool LOSS, int SPLIT>
-__global__ void __launch_bounds__(FW_THREADS) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int n_tiles, int *tile_bins,
+__global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int n_tiles, int *tile_bins,
                                                                 const float4 *__restrict__ packed, GatherSrc src,
                                                                 const int *__restrict__ d_status,
                                                                 const float *__restrict__ background, float *__restrict__ out_img,
                                                                 float *__restrict__ final_Ts, int *__restrict__ final_idx,
-                                                                float *out_mc, int vec_ok, LossArgs la = LossArgs{}) {
+                                                                float *out_mc, int vec_ok, LossArgs la = LossArgs{},
+                                                                PeerOut peers = PeerOut{}) {
     constexpr int ISHIFT = SPLIT == 2 ? 1 : 0;
     constexpr int BW = 4 / SPLIT;                         // pixels per lane and row
     constexpr int XSH = SPLIT == 2 ? 1 : 2;               // log2(BW)
@@ -218,8 +228,9 @@ __global__ void __launch_bounds__(FW_THREADS) raster_fwd_kernel(int TX, int W, i
     const int first = warp * G + blockIdx.x, n_items = n_tiles << ISHIFT;
     ChunkPipe pipe;
     pipe.init(tile_bins, packed, reinterpret_cast<float4 *>(fw_smem) + (size_t)warp * PIPE_NST * PIPE_CHUNK * 3,
-              reinterpret_cast<uint64_t *>(fw_smem + (size_t)FW_WARPS * PIPE_NST * PIPE_CHUNK * 48) + warp * PIPE_NST, tile_begin, n_tiles,
+              reinterpret_cast<uint64_t *>(fw_smem + FW_RING_BYTES + FW_OUT_BYTES) + warp * PIPE_NST, tile_begin, n_tiles,
               ISHIFT, false, first, stride, lane, TMA);
+    float4 *const s_out4 = reinterpret_cast<float4 *>(fw_smem + FW_RING_BYTES) + (size_t)warp * (GI2D_TILE_PIX * 3 / 4);
     const int part = first & (SPLIT - 1);                 // which half of its tiles this warp renders (constant: stride is even)
 
     float sq_sum = 0.f;                                    // LOSS: this thread's share of the squared error
@@ -367,20 +378,17 @@ __global__ void __launch_bounds__(FW_THREADS) raster_fwd_kernel(int TX, int W, i
                 }
             }
             if (vec_tile) {
+                // stage the lane's run into the warp's output tile (rows of 48 floats): the tile then leaves as whole 192-byte
+                // rows, 12 consecutive lanes on 12 consecutive float4 -- full sectors for the L2 and, with a multicast
+                // address, full-size NVLink write packets instead of scattered 16-byte ones
+                float *const so = reinterpret_cast<float *>(s_out4) + (row0 + 2 * bym + r) * (GI2D_TILE * 3) + 3 * BW * bxm;
                 if (BW == 4) {
 #pragma unroll
-                    for (int k4 = 0; k4 < 3; ++k4) {
-                        const float4 o4 = make_float4(v[4 * k4], v[4 * k4 + 1], v[4 * k4 + 2], v[4 * k4 + 3]);
-                        if (out_mc) multimem_st_v4(out_mc + 3 * pix0 + 4 * k4, o4);
-                        else *reinterpret_cast<float4 *>(dst_img + 3 * pix0 + 4 * k4) = o4;
-                    }
-                } else {                                   // 2 pixels = 24 contiguous bytes, 8-byte aligned
+                    for (int k4 = 0; k4 < 3; ++k4)
+                        reinterpret_cast<float4 *>(so)[k4] = make_float4(v[4 * k4], v[4 * k4 + 1], v[4 * k4 + 2], v[4 * k4 + 3]);
+                } else {
 #pragma unroll
-                    for (int k2 = 0; k2 < 3; ++k2) {
-                        const float2 o2 = make_float2(v[2 * k2], v[2 * k2 + 1]);
-                        if (out_mc) multimem_st_v2(out_mc + 3 * pix0 + 2 * k2, o2);
-                        else *reinterpret_cast<float2 *>(dst_img + 3 * pix0 + 2 * k2) = o2;
-                    }
+                    for (int k2 = 0; k2 < 3; ++k2) reinterpret_cast<float2 *>(so)[k2] = make_float2(v[2 * k2], v[2 * k2 + 1]);
                 }
             } else if (i < H) {
 #pragma unroll
@@ -401,6 +409,20 @@ __global__ void __launch_bounds__(FW_THREADS) raster_fwd_kernel(int TX, int W, i
                         final_idx[pix0 + c] = cur[r][c];
                     }
             }
+        }
+        if (vec_tile) {
+            __syncwarp();
+            constexpr int F4_ROW = GI2D_TILE * 3 / 4, F4_PART = ROWS * F4_ROW;            // 12 float4 per row; 192 / 96 per part
+#pragma unroll
+            for (int jj = 0; jj < F4_PART / 32; ++jj) {
+                const int idx = jj * 32 + lane, rr = idx / F4_ROW, c4 = idx - rr * F4_ROW;
+                const float4 o4 = s_out4[row0 * F4_ROW + idx];
+                const size_t off = ((size_t)(ty0 + row0 + rr) * W + tx0) * 3 + 4 * c4;
+                if (out_mc) multimem_st_v4(out_mc + off, o4);
+                else *reinterpret_cast<float4 *>(dst_img + off) = o4;
+                for (int pk = 0; pk < peers.n; ++pk) __stcs(reinterpret_cast<float4 *>(peers.p[pk] + off), o4);
+            }
+            __syncwarp();                                  // the staging tile is free for the next tile
         }
     }
     if (LOSS) {
@@ -731,6 +753,7 @@ struct FwdArgs {
     float *out_mc;
     int vec_ok;
     LossArgs la;
+    PeerOut peers;
 };
 template <bool TMA, bool AUX, bool LOSS>
 static int fwd_grid_for(int n_tiles) {
@@ -741,10 +764,10 @@ static void launch_fwd(const FwdArgs &a, cudaStream_t stream) {
     const int grid = fwd_grid_for<TMA, AUX, LOSS>(a.n_tiles);
     if (fwd_split(a.n_tiles) == 2)
         raster_fwd_kernel<TMA, AUX, LOSS, 2><<<grid, FW_THREADS, FW_SMEM, stream>>>(a.TX, a.W, a.H, a.tile_begin, a.n_tiles, a.tile_bins, a.packed, a.src, a.d_status,
-                                                                                   a.background, a.out_img, a.final_Ts, a.final_idx, a.out_mc, a.vec_ok, a.la);
+                                                                                   a.background, a.out_img, a.final_Ts, a.final_idx, a.out_mc, a.vec_ok, a.la, a.peers);
     else
         raster_fwd_kernel<TMA, AUX, LOSS, 1><<<grid, FW_THREADS, FW_SMEM, stream>>>(a.TX, a.W, a.H, a.tile_begin, a.n_tiles, a.tile_bins, a.packed, a.src, a.d_status,
-                                                                                   a.background, a.out_img, a.final_Ts, a.final_idx, a.out_mc, a.vec_ok, a.la);
+                                                                                   a.background, a.out_img, a.final_Ts, a.final_idx, a.out_mc, a.vec_ok, a.la, a.peers);
 }
 template <typename K>
 static int bwd_grid(K kernel, int n_items) { return persistent_grid(kernel, BW_THREADS, BW_SMEM, n_items, "GI2D_BWD_CTAS_PER_SM"); }
@@ -776,7 +799,7 @@ int gi2d_raster_sum_fwd(int TX, int TY, int W, int H, const int *gids_sorted, co
     if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0) return GI2D_ERR_INVALID;
     GatherSrc src{gids_sorted, xys, conics, colors, opacities};
     const FwdArgs a{TX, W, H, 0, TX * TY, const_cast<int *>(tile_bins), nullptr, src, nullptr, nullptr, out_img, final_Ts, final_idx, nullptr,
-                    vec_ok(W, out_img), LossArgs{}};
+                    vec_ok(W, out_img), LossArgs{}, PeerOut{}};
     if (final_Ts && final_idx) launch_fwd<false, true, false>(a, stream);
     else launch_fwd<false, false, false>(a, stream);
     return cuda_status();
@@ -792,9 +815,32 @@ int gi2d_raster_sum_fwd_packed_rows_mc(int TX, int TY, int W, int H, int ty_begi
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     const float4 *p = reinterpret_cast<const float4 *>(packed);
     const int nt = (ty_end - ty_begin) * TX, first = ty_begin * TX;
-    const FwdArgs a{TX, W, H, first, nt, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx, out_img_mc, vok, LossArgs{}};
+    const FwdArgs a{TX, W, H, first, nt, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx, out_img_mc, vok, LossArgs{}, PeerOut{}};
     if (final_Ts && final_idx) launch_fwd<true, true, false>(a, stream);
     else launch_fwd<true, false, false>(a, stream);
+    return cuda_status();
+}
+
+// Row-sharded variant with the all-gather fused into the rasterizer by PEER STORES: every full-tile row is stored to out_img
+// and to the same offset of each of the n_peers (<= 7) frame buffers in `peer_imgs` (HOST array of peer-mapped DEVICE
+// addresses).  Requires W % 4 == 0, 16-byte aligned buffers and an image of whole tiles (ragged tiles are stored locally only).
+int gi2d_raster_sum_fwd_packed_rows_p2p(int TX, int TY, int W, int H, int ty_begin, int ty_end, int *tile_bins, const float *packed,
+                                        float *out_img, float *const *peer_imgs, int n_peers, cudaStream_t stream) {
+    if (TX <= 0 || TY <= 0 || W <= 0 || H <= 0 || ty_begin < 0 || ty_end > TY || ty_begin >= ty_end || n_peers < 0 || n_peers > 7 ||
+        (n_peers && !peer_imgs))
+        return GI2D_ERR_INVALID;
+    int vok = vec_ok(W, out_img);
+    PeerOut po{};
+    po.n = n_peers;
+    for (int k = 0; k < n_peers; ++k) {
+        po.p[k] = peer_imgs[k];
+        vok = vok && vec_ok(W, peer_imgs[k]);
+    }
+    if (n_peers && !vok) return GI2D_ERR_INVALID;
+    GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
+    const FwdArgs a{TX, W, H, ty_begin * TX, (ty_end - ty_begin) * TX, tile_bins, reinterpret_cast<const float4 *>(packed), src, nullptr, nullptr,
+                    out_img, nullptr, nullptr, nullptr, vok, LossArgs{}, po};
+    launch_fwd<true, false, false>(a, stream);
     return cuda_status();
 }
 
@@ -874,7 +920,7 @@ int gi2d_raster_sum_fwd_packed_mse(int TX, int TY, int W, int H, int *tile_bins,
                 reinterpret_cast<float *>(reinterpret_cast<char *>(ws) + 16), reinterpret_cast<unsigned int *>(ws), loss};
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     const FwdArgs a{TX, W, H, 0, nt, tile_bins, reinterpret_cast<const float4 *>(packed), src, d_status, background, nullptr, nullptr, nullptr,
-                    nullptr, vec_ok(W, v_out), la};
+                    nullptr, vec_ok(W, v_out), la, PeerOut{}};
     launch_fwd<true, false, true>(a, stream);
     return cuda_status();
 }

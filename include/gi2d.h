@@ -225,6 +225,13 @@ int gi2d_raster_sum_fwd_packed_rows_mc(int TX, int TY, int W, int H, int ty_begi
                                        const float *packed, const int *d_status, const float *background, float *out_img,
                                        float *out_img_mc, float *final_Ts, int *final_idx, cudaStream_t stream);
 
+/* Row-sharded variant with the all-gather fused into the rasterizer by PEER STORES over NVLink: every full-tile row goes to
+ * out_img and to the same offset of each of the n_peers (<= 7) frame buffers of the other ranks, `peer_imgs` being a HOST
+ * array of peer-mapped DEVICE addresses (e.g. torch symmetric memory's buffer_ptrs).  W % 4 == 0 and 16-byte aligned
+ * buffers are required when n_peers > 0; the image must consist of whole tiles (ragged tiles are stored locally only). */
+int gi2d_raster_sum_fwd_packed_rows_p2p(int TX, int TY, int W, int H, int ty_begin, int ty_end, int *tile_bins, const float *packed,
+                                        float *out_img, float *const *peer_imgs, int n_peers, cudaStream_t stream);
+
 /* Replaces rasterize_sum_backward (ext.cpp:23 -> bindings.cu:706-779 -> backward.cu:696-862).
  * v_out (H,W,3).  Outputs v_xy (N,2), v_conic (N,3), v_colors (N,3), v_opacity (N,1) are zeroed by the call.
  * final_idx is accepted for parity and may be NULL.  fp32 atomic accumulation (order-nondeterministic, as in the
