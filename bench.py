@@ -963,11 +963,9 @@ def measure_decode8k(args, rank, world, dev, K, Wm, with_e2e=True):
         with ClockSampler(dev.index) as clk:
             total_ms = K * pipeline_ms(lambda: R.render_compressed_async(d_in[0], d_in[1], scale, beta, bound, d_in[2], cb, opacity),
                                        R.wait_frames)
-        serial_ts = timed_replays(decode, K, flush)                 # one frame at a time, L2 flushed in between (round-1 protocol)
-        serial_ms = torch.tensor([sum(serial_ts) / K], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(serial_ms, op=dist.ReduceOp.MAX)
-        serial_ms = serial_ms.item()
+        serial_ms = None
+        if world == 1:             # one frame at a time, L2 flushed in between (the round-1 protocol), single GPU only
+            serial_ms = sum(timed_replays(decode, K, flush)) / K
         if R is not R_nccl:        # the plain NCCL variant beside it, same protocol
             nccl_ms = pipeline_ms(lambda: decode(R_nccl), lambda: None)
         p2p_ms = None

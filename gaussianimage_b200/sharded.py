@@ -86,9 +86,13 @@ class RowShardedRenderer:
                 self._peers.append((C.c_void_p * max(len(ptrs), 1))(*ptrs))
                 if exchange == "ce":
                     self._peer_bufs = getattr(self, "_peer_bufs", [])
-                    self._peer_bufs.append([hdl.get_buffer(k, shape, torch.float32) for k in range(self.world) if k != self.rank])
+                    # rank r pushes to r+1, r+2, ...: at every step the copies of all ranks form a permutation, so no
+                    # destination receives from two sources at once
+                    self._peer_bufs.append([hdl.get_buffer((self.rank + k) % self.world, shape, torch.float32)
+                                            for k in range(1, self.world)])
             self.fused = True
             self._side = torch.cuda.Stream(device=self.device)
+            self._side2 = torch.cuda.Stream(device=self.device)      # second copy queue of the copy-engine exchange
             self._done = [torch.cuda.Event(), torch.cuda.Event()]
             torch.cuda.synchronize(self.device)
             self._hdls[0].barrier(channel=0)            # every rank's buffers are zeroed before anybody's stores arrive
@@ -192,8 +196,21 @@ class RowShardedRenderer:
             if self.exchange == "ce":       # (the side stream is ordered: these copies follow the barrier of the previous frame)
                 lo, hi = self.rank * self.band_rows, (self.rank + 1) * self.band_rows
                 mine = self.buffers[b][lo:hi]
-                for peer in self._peer_bufs[b]:
-                    peer[lo:hi].copy_(mine, non_blocking=True)
+                peers = self._peer_bufs[b]
+                if len(peers) > 1:          # two copy queues, so that two copy engines keep the links busy back to back
+                    go = torch.cuda.Event()
+                    go.record(self._side)
+                    with torch.cuda.stream(self._side2):
+                        self._side2.wait_event(go)
+                        for peer in peers[1::2]:
+                            peer[lo:hi].copy_(mine, non_blocking=True)
+                        back = torch.cuda.Event()
+                        back.record(self._side2)
+                    for peer in peers[0::2]:
+                        peer[lo:hi].copy_(mine, non_blocking=True)
+                    self._side.wait_event(back)
+                else:
+                    peers[0][lo:hi].copy_(mine, non_blocking=True)
             self._hdls[b].barrier(channel=0)
             self._done[b].record(self._side)
 

@@ -720,3 +720,107 @@ def test_cpp_autograd_functions_pass_the_operator_level_suite():
                         "tests/test_gpu_loss.py", "tests/test_gpu_fit.py", "-q", "-x", "-m", "gpu", "-k", sel, "-p", "no:cacheprovider"],
                        env={**os.environ, "GI2D_CPP_AUTOGRAD": other}, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+# ------------------------------------------------------------------------------- round-2 ABI additions
+def test_projection_publishes_the_intersection_total():
+    """gi2d_project_fwd_total: sum(num_tiles_hit) -- what compute_cumulative_intersects reads with `.item()`
+    (gsplat/gsplat/utils.py:116-118) -- arrives in a device word and in mapped pinned host memory, for both
+    parametrisations, repeatedly (the library-owned ticket words must be left clean by every launch)."""
+    from gaussianimage_b200._lib import check, lib
+    L = lib()
+    st = torch.cuda.current_stream().cuda_stream
+    host = torch.full((4,), -1, dtype=torch.int32).pin_memory()
+    for name in ("ragged", "c1_small", "dense"):
+        s = scene(name)
+        d = s.to(DEV)
+        N = d.means2d.shape[0]
+        TX, TY, _ = s.tile_bounds
+        for mode, pa, pb in ((0, d.cholesky, None), (1, d.scales, d.rotation)):
+            for rep in range(3):
+                xys, depths = torch.empty(N, 2, device=DEV), torch.empty(N, device=DEV)
+                radii, nth = torch.empty(N, dtype=torch.int32, device=DEV), torch.empty(N, dtype=torch.int32, device=DEV)
+                conics = torch.empty(N, 3, device=DEV)
+                tot = torch.full((1,), -5, dtype=torch.int32, device=DEV)
+                host[rep] = -1
+                check(L.gi2d_project_fwd_total(mode, N, d.means2d.data_ptr(), pa.data_ptr(), 0 if pb is None else pb.data_ptr(), s.H, s.W,
+                                               TX, TY, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), conics.data_ptr(),
+                                               nth.data_ptr(), tot.data_ptr(), host.data_ptr() + 4 * rep, st), "project_fwd_total")
+                torch.cuda.synchronize()
+                want = int(nth.sum().item())
+                assert int(tot.item()) == want and int(host[rep]) == want
+                ref = (G.project_gaussians_2d(d.means2d, d.cholesky, s.H, s.W, s.tile_bounds) if mode == 0 else
+                       G.project_gaussians_2d_scale_rot(d.means2d, d.scales, d.rotation, s.H, s.W, s.tile_bounds))
+                assert torch.equal(xys, ref[0]) and torch.equal(radii, ref[2]) and torch.equal(conics, ref[3]) and torch.equal(nth, ref[4])
+
+
+def test_second_backward_through_the_same_graph_matches_the_first():
+    """The gradient rows are zero-filled by the forward's binning chain and accumulated into ONCE; a second backward through the
+    same node (retain_graph) must take the allocating path and give the same gradients."""
+    s = scene("c1_small")
+    d = s.to(DEV)
+    means = d.means2d.clone().requires_grad_(True)
+    L = d.cholesky.clone().requires_grad_(True)
+    colors = d.colors.clone().requires_grad_(True)
+    pr = G.project_gaussians_2d(means, L, s.H, s.W, s.tile_bounds)
+    out = G.rasterize_gaussians_sum(*pr, colors, d.opacity, s.H, s.W)
+    loss = torch.nn.functional.mse_loss(out, d.gt)
+    g1 = torch.autograd.grad(loss, [means, L, colors], retain_graph=True)
+    g2 = torch.autograd.grad(loss, [means, L, colors])
+    for a, b, nm in zip(g1, g2, ("means", "L", "colors")):
+        assert_grad_close(_np(b), _np(a), f"second backward, {nm}")
+
+
+def test_two_streams_bin_concurrently_without_sharing_barrier_words():
+    """The one-kernel binning's grid barrier lives on library-owned words; every launch gets its own pair (csrc/api.cu:
+    sync_slot), so two streams running the kernel at the same moment cannot release each other's barrier."""
+    from gaussianimage_b200._lib import check, lib
+    L = lib()
+    s = make_scene(96, 128, 1500, seed=8)          # small grids: two of them are co-resident
+    d = s.to(DEV)
+    xys, depths, radii, conics, nth = G.project_gaussians_2d(d.means2d, d.cholesky, s.H, s.W, s.tile_bounds)
+    N, (TX, TY, _) = xys.shape[0], s.tile_bounds
+    cap = int(nth.sum().item()) + 64
+    want = None
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    bufs = []
+    for _ in streams:
+        nbytes = L.gi2d_bin_fused_workspace_bytes(N, TX, TY, cap)
+        bufs.append(dict(ws=torch.empty(nbytes, dtype=torch.uint8, device=DEV), gids=torch.empty(cap, dtype=torch.int32, device=DEV),
+                         bins=torch.empty(TX * TY, 2, dtype=torch.int32, device=DEV), packed=torch.empty(cap * 12, device=DEV),
+                         status=torch.empty(2, dtype=torch.int32, device=DEV), nbytes=nbytes))
+    torch.cuda.synchronize()
+    for it in range(200):
+        for stv, b in zip(streams, bufs):
+            check(L.gi2d_bin_fused(N, TX, TY, xys.data_ptr(), radii.data_ptr(), nth.data_ptr(), conics.data_ptr(), d.colors.data_ptr(),
+                                   d.opacity.data_ptr(), cap, b["ws"].data_ptr(), b["nbytes"], b["gids"].data_ptr(), b["bins"].data_ptr(),
+                                   b["packed"].data_ptr(), b["status"].data_ptr(), stv.cuda_stream), "bin_fused")
+        if it % 50 == 49:
+            torch.cuda.synchronize()
+            for b in bufs:
+                n = int(b["status"][0].item())
+                got = b["gids"][:n].clone()
+                if want is None:
+                    want = got
+                assert torch.equal(got, want)
+    _, st = oracle_chain(s)
+    assert np.array_equal(_np(want), st["gaussian_ids_sorted"])
+
+
+def test_peer_store_epilogue_writes_every_frame_buffer():
+    """gi2d_raster_sum_fwd_packed_rows_p2p: the row-sharded rasterizer stores every full-tile row to its own frame buffer AND
+    to the peer buffers it is given (a second local buffer stands in for another rank's peer-mapped one)."""
+    import ctypes as C
+    from gaussianimage_b200._lib import check, lib
+    L = lib()
+    s = make_scene(128, 192, 3000, seed=4)           # whole tiles, W % 4 == 0
+    d = s.to(DEV)
+    f = _fused_internals(d, s)
+    TX, TY, _ = s.tile_bounds
+    mine, peer = torch.zeros(s.H, s.W, 3, device=DEV), torch.zeros(s.H, s.W, 3, device=DEV)
+    ptrs = (C.c_void_p * 1)(peer.data_ptr())
+    for r0, r1 in ((0, 3), (3, TY)):
+        check(L.gi2d_raster_sum_fwd_packed_rows_p2p(TX, TY, s.W, s.H, r0, r1, f["tile_bins"].data_ptr(), f["packed"].data_ptr(),
+                                                    mine.data_ptr(), ptrs, 1, torch.cuda.current_stream().cuda_stream), "p2p rows")
+    torch.cuda.synchronize()
+    assert torch.equal(mine, f["out"]) and torch.equal(peer, f["out"])
