@@ -653,7 +653,7 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
     if (a.dbg & 16) return;
     // grid-wide barrier (cooperative launch: all blocks are co-resident, the barrier state belongs to the driver, so
     // this path needs no zero-initialised memory at all)
-    __threadfence();
+    if (!a.bar || (a.dbg & 128)) __threadfence();       // own barrier: its release (after the block barrier) is cumulative over the block's writes
     if (a.bar) grid_barrier(a.bar, gridDim.x); else cooperative_groups::this_grid().sync();
     // ---- phase 3a: exclusive scan over the BLOCKS of every tile column, in place.  A warp takes FOUR adjacent columns
     // (16 bytes of every row) and splits the rows into eight contiguous groups, one per quarter-warp row of lanes: each
@@ -706,7 +706,7 @@ __global__ void __launch_bounds__(NT, 1) bin_small_kernel(SmallArgs a) {
             if (rgrp == 0) a.tot[item * 4 + c4] = total;
         }
     }
-    __threadfence();
+    if (!a.bar || (a.dbg & 128)) __threadfence();
     if (a.bar) grid_barrier(a.bar, gridDim.x); else cooperative_groups::this_grid().sync();
     if (a.dbg & 64) return;
     // ---- phase 3b: first slot of every tile = exclusive scan of the totals in tile order + the preceding blocks
