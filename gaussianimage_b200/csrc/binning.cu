@@ -1061,49 +1061,96 @@ __device__ __forceinline__ void warp_bitonic(int *buf, int L) {
 
 constexpr int SORT_SMEM = 512;     // gids per warp sorted in shared memory
 
+constexpr int SORT_TPW = 2;         // tiles per warp, handled in lockstep: twice the loads in flight per warp (the kernel is latency-bound)
+
 __global__ void __launch_bounds__(256) tile_sort_pack_kernel(ScatterArgs a) {
     __shared__ int s_buf[8][SORT_SMEM];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int tile = blockIdx.x * 8 + warp;
-    if (tile >= a.T) return;
+    const int tile0 = (blockIdx.x * 8 + warp) * SORT_TPW;
+    if (tile0 >= a.T) return;
     const int cap = a.capacity;
-    const int lo = min(tile ? (int)min(a.cur[tile - 1], (uint32_t)0x7fffffff) : 0, cap);
-    const int hi = min((int)min(a.cur[tile], (uint32_t)0x7fffffff), cap);
-    const int L = hi - lo;
-    if (lane == 0) reinterpret_cast<int2 *>(a.tile_bins)[tile] = L > 0 ? make_int2(lo, hi) : make_int2(0, 0);
-    if (L <= 0) return;
-    int *g = a.gids_sorted + lo;
-    auto put_record = [&](int slot, int v) {
+    int lo[SORT_TPW], L[SORT_TPW];
+    {   // ranges of the warp's consecutive tiles: cur[] holds the END of every tile after the scatter pass
+        uint32_t e[SORT_TPW + 1];
+        e[0] = tile0 ? a.cur[tile0 - 1] : 0u;
+#pragma unroll
+        for (int q = 0; q < SORT_TPW; ++q) e[q + 1] = tile0 + q < a.T ? a.cur[tile0 + q] : e[q];
+#pragma unroll
+        for (int q = 0; q < SORT_TPW; ++q) {
+            lo[q] = min((int)min(e[q], (uint32_t)0x7fffffff), cap);
+            L[q] = min((int)min(e[q + 1], (uint32_t)0x7fffffff), cap) - lo[q];
+            if (lane == 0 && tile0 + q < a.T)
+                reinterpret_cast<int2 *>(a.tile_bins)[tile0 + q] = L[q] > 0 ? make_int2(lo[q], lo[q] + L[q]) : make_int2(0, 0);
+        }
+    }
+    auto put_record = [&](int base, int slot, int v) {
         const float4 *row = a.rows + 3 * (size_t)v;
         const float4 r0 = __ldg(row), r1 = __ldg(row + 1), r2 = __ldg(row + 2);
-        float4 *dst = a.packed + 3 * (size_t)(lo + slot);
+        float4 *dst = a.packed + 3 * (size_t)(base + slot);
         __stcs(dst + 0, r0);
         __stcs(dst + 1, r1);
         __stcs(dst + 2, r2);
     };
-    if (L <= 32) {                                  // one gid per lane: its rank is its slot, nothing is re-read
-        const int v = lane < L ? g[lane] : 0x7fffffff;
-        int rank = 0;
-        for (int k = 0; k < L; ++k) rank += __shfl_sync(0xffffffffu, v, k) < v;
-        if (lane < L) {
-            g[rank] = v;
-            put_record(rank, v);
+    bool all_small = true;
+#pragma unroll
+    for (int q = 0; q < SORT_TPW; ++q) all_small = all_small && L[q] <= 32;
+    if (all_small) {                                // one gid per lane and tile: its rank is its slot, nothing is re-read
+        int v[SORT_TPW], rank[SORT_TPW], Lmax = 0;
+#pragma unroll
+        for (int q = 0; q < SORT_TPW; ++q) {
+            v[q] = lane < L[q] ? a.gids_sorted[lo[q] + lane] : 0x7fffffff;       // the loads of all tiles are in flight together
+            rank[q] = 0;
+            Lmax = max(Lmax, L[q]);
         }
+        for (int k = 0; k < Lmax; ++k) {
+#pragma unroll
+            for (int q = 0; q < SORT_TPW; ++q) rank[q] += __shfl_sync(0xffffffffu, v[q], k) < v[q];    // (+inf padding never counts)
+        }
+        float4 r[SORT_TPW][3];
+#pragma unroll
+        for (int q = 0; q < SORT_TPW; ++q)
+            if (lane < L[q]) {
+                const float4 *row = a.rows + 3 * (size_t)v[q];
+                r[q][0] = __ldg(row); r[q][1] = __ldg(row + 1); r[q][2] = __ldg(row + 2);
+            }
+#pragma unroll
+        for (int q = 0; q < SORT_TPW; ++q)
+            if (lane < L[q]) {
+                a.gids_sorted[lo[q] + rank[q]] = v[q];
+                float4 *dst = a.packed + 3 * (size_t)(lo[q] + rank[q]);
+                __stcs(dst + 0, r[q][0]); __stcs(dst + 1, r[q][1]); __stcs(dst + 2, r[q][2]);
+            }
         return;
     }
-    const int *src = g;
-    if (L <= SORT_SMEM) {
-        for (int k = lane; k < L; k += 32) s_buf[warp][k] = g[k];
+    for (int q = 0; q < SORT_TPW; ++q) {            // a longer list among them: one tile after the other
+        if (L[q] <= 0) continue;
+        int *g = a.gids_sorted + lo[q];
+        if (L[q] <= 32) {
+            const int v = lane < L[q] ? g[lane] : 0x7fffffff;
+            int rank = 0;
+            for (int k = 0; k < L[q]; ++k) rank += __shfl_sync(0xffffffffu, v, k) < v;
+            __syncwarp();
+            if (lane < L[q]) {
+                g[rank] = v;
+                put_record(lo[q], rank, v);
+            }
+            continue;
+        }
+        const int *src = g;
+        if (L[q] <= SORT_SMEM) {
+            for (int k = lane; k < L[q]; k += 32) s_buf[warp][k] = g[k];
+            __syncwarp();
+            warp_bitonic(s_buf[warp], L[q]);
+            for (int k = lane; k < L[q]; k += 32) g[k] = s_buf[warp][k];
+            src = s_buf[warp];
+        } else {
+            __syncwarp();
+            warp_bitonic(g, L[q]);                   // rare: a tile with more than 512 intersections
+        }
         __syncwarp();
-        warp_bitonic(s_buf[warp], L);
-        for (int k = lane; k < L; k += 32) g[k] = s_buf[warp][k];
-        src = s_buf[warp];
-    } else {
-        __syncwarp();
-        warp_bitonic(g, L);                          // rare: a tile with more than 512 intersections
+        for (int k = lane; k < L[q]; k += 32) put_record(lo[q], k, src[k]);
+        __syncwarp();                                // s_buf is reused by the next tile of this warp
     }
-    __syncwarp();
-    for (int k = lane; k < L; k += 32) put_record(k, src[k]);
 }
 
 // Records of an EXISTING sorted list with other per-Gaussian attributes: a caller that renders the same geometry several
@@ -1311,7 +1358,7 @@ static int bin_fused_impl(int N, int TX, int TY, int ty_begin, int ty_end, const
         tile_count_scatter_kernel<false><<<gblocks, 256, 0, stream>>>(a);
         tile_scan_kernel<1024><<<sblocks, 1024, 0, stream>>>(a, all_resident(tile_scan_kernel<1024>, 1024, sblocks) ? 0 : 1);
         tile_count_scatter_kernel<true><<<gblocks, 256, 0, stream>>>(a);
-        tile_sort_pack_kernel<<<(T + 7) / 8, 256, 0, stream>>>(a);
+        tile_sort_pack_kernel<<<(T + 8 * SORT_TPW - 1) / (8 * SORT_TPW), 256, 0, stream>>>(a);
         return cuda_status();
     }
 

@@ -124,14 +124,14 @@ __global__ void __launch_bounds__(PB) project_fwd_kernel(int N, const float *__r
             int b = 0;
 #pragma unroll
             for (int k = 0; k < PB / 32; ++k) b += s_sum[k];
-            atomicAdd(total_slot, (unsigned int)b);
-            __threadfence();
-            if (atomicAdd(total_slot + 1, 1u) == gridDim.x - 1) {
-                __threadfence();
-                const int total = (int)atomicExch(total_slot, 0u);
-                total_slot[1] = 0u;
+            // ONE 64-bit atomic per block on the pair of words: low word += block sum, high word += 1 (arrivals)
+            unsigned long long *pair = reinterpret_cast<unsigned long long *>(total_slot);
+            const unsigned long long old = atomicAdd(pair, (1ull << 32) | (unsigned long long)(unsigned int)b);
+            if ((unsigned int)(old >> 32) == gridDim.x - 1) {             // last block: total complete, leave the pair zero
+                const int total = (int)((unsigned int)old + (unsigned int)b);
+                atomicExch(pair, 0ull);
                 if (total_dev) *total_dev = total;
-                if (total_host) { __threadfence_system(); *total_host = total; }
+                if (total_host) *total_host = total;        // the word stands alone: nothing else has to be visible with it
             }
         }
     }

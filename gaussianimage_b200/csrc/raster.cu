@@ -200,14 +200,17 @@ constexpr int FW_CHUNK = PIPE_CHUNK;
 constexpr int FW_THREADS = FW_WARPS * 32;
 constexpr size_t FW_RING_BYTES = (size_t)FW_WARPS * PIPE_NST * PIPE_CHUNK * 48;
 constexpr size_t FW_OUT_BYTES = (size_t)FW_WARPS * GI2D_TILE_PIX * 3 * 4;        // one output tile per warp (epilogue staging)
-constexpr size_t FW_SMEM = FW_RING_BYTES + FW_OUT_BYTES + (size_t)FW_WARPS * PIPE_NST * 8;
+constexpr size_t FW_SMEM = FW_RING_BYTES + (size_t)FW_WARPS * PIPE_NST * 8;
+constexpr size_t FW_SMEM_EXCH = FW_SMEM + FW_OUT_BYTES;
 
 // SPLIT = 1: a warp renders a whole tile, a lane a 4x2 pixel block (images with many tiles: 8K decode).
 // SPLIT = 2: a warp renders HALF a tile (8 pixel rows), a lane a 2x2 block; the two halves of a tile go to different
 //            warps (different CTAs), each streaming the tile's records itself -- twice the warps for the fitting images
 //            (768x512 has only 1536 tiles for 148 SMs), the same instruction count (finer culling pays for the second
 //            set of masks).
-template <bool TMA, bool AUX, bool LOSS, int SPLIT>
+// EXCH: the frame buffers of other ranks are written too (NVLS multicast address or peer-mapped buffers): the output tile is
+//       staged in shared memory and leaves as whole 192-byte rows.
+template <bool TMA, bool AUX, bool LOSS, int SPLIT, bool EXCH = false>
 __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W, int H, int tile_begin, int n_tiles, int *tile_bins,
                                                                 const float4 *__restrict__ packed, GatherSrc src,
                                                                 const int *__restrict__ d_status,
@@ -228,9 +231,9 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
     const int first = warp * G + blockIdx.x, n_items = n_tiles << ISHIFT;
     ChunkPipe pipe;
     pipe.init(tile_bins, packed, reinterpret_cast<float4 *>(fw_smem) + (size_t)warp * PIPE_NST * PIPE_CHUNK * 3,
-              reinterpret_cast<uint64_t *>(fw_smem + FW_RING_BYTES + FW_OUT_BYTES) + warp * PIPE_NST, tile_begin, n_tiles,
+              reinterpret_cast<uint64_t *>(fw_smem + FW_RING_BYTES + (EXCH ? FW_OUT_BYTES : 0)) + warp * PIPE_NST, tile_begin, n_tiles,
               ISHIFT, false, first, stride, lane, TMA);
-    float4 *const s_out4 = reinterpret_cast<float4 *>(fw_smem + FW_RING_BYTES) + (size_t)warp * (GI2D_TILE_PIX * 3 / 4);
+    float4 *const s_out4 = reinterpret_cast<float4 *>(fw_smem + FW_RING_BYTES) + (size_t)warp * (GI2D_TILE_PIX * 3 / 4);   // EXCH only
     const int part = first & (SPLIT - 1);                 // which half of its tiles this warp renders (constant: stride is even)
 
     float sq_sum = 0.f;                                    // LOSS: this thread's share of the squared error
@@ -268,9 +271,10 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                 gather_chunk(rec, src, lo + off, n, lane);
             }
             // which records of the chunk touch this lane's pixel block: 64-bit mask from 2 x (NBX + NBY = 12) ballots
-            uint32_t m[2];
+            uint32_t m[2] = {0u, 0u};
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
+                if (h == 1 && n <= 32) break;              // sparse tiles (8K decode: ~19 records per tile): one round of ballots
                 const int t = 32 * h + lane;
                 uint32_t colbits = 0, rowbits = 0;
                 if (t < n) {
@@ -348,6 +352,7 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
         // into the frame buffer of EVERY rank -- the all-gather of a row-sharded render happens inside the rasterizer.
         float *const dst_img = LOSS ? la.v_out : out_img;
         const bool vec_tile = vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H;     // uniform over the warp
+        constexpr bool staged = EXCH;
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
             const int i = ty0 + row0 + 2 * bym + r, j0 = tx0 + BW * bxm;
@@ -377,10 +382,10 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                     }
                 }
             }
-            if (vec_tile) {
-                // stage the lane's run into the warp's output tile (rows of 48 floats): the tile then leaves as whole 192-byte
-                // rows, 12 consecutive lanes on 12 consecutive float4 -- full sectors for the L2 and, with a multicast
-                // address, full-size NVLink write packets instead of scattered 16-byte ones
+            if (vec_tile && staged) {
+                // frame buffers of other ranks are written too (multicast / peer stores): stage the lane's run into the warp's
+                // output tile (rows of 48 floats); the tile then leaves as whole 192-byte rows, 12 consecutive lanes on 12
+                // consecutive float4 -- full-size NVLink write packets instead of scattered 16-byte ones
                 float *const so = reinterpret_cast<float *>(s_out4) + (row0 + 2 * bym + r) * (GI2D_TILE * 3) + 3 * BW * bxm;
                 if (BW == 4) {
 #pragma unroll
@@ -389,6 +394,16 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                 } else {
 #pragma unroll
                     for (int k2 = 0; k2 < 3; ++k2) reinterpret_cast<float2 *>(so)[k2] = make_float2(v[2 * k2], v[2 * k2 + 1]);
+                }
+            } else if (vec_tile) {                         // local image only: the lane's 12 * BW contiguous bytes, straight from registers
+                if (BW == 4) {
+#pragma unroll
+                    for (int k4 = 0; k4 < 3; ++k4)
+                        *reinterpret_cast<float4 *>(dst_img + 3 * pix0 + 4 * k4) = make_float4(v[4 * k4], v[4 * k4 + 1], v[4 * k4 + 2], v[4 * k4 + 3]);
+                } else {
+#pragma unroll
+                    for (int k2 = 0; k2 < 3; ++k2)
+                        *reinterpret_cast<float2 *>(dst_img + 3 * pix0 + 2 * k2) = make_float2(v[2 * k2], v[2 * k2 + 1]);
                 }
             } else if (i < H) {
 #pragma unroll
@@ -410,7 +425,7 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                     }
             }
         }
-        if (vec_tile) {
+        if (vec_tile && staged) {
             __syncwarp();
             constexpr int F4_ROW = GI2D_TILE * 3 / 4, F4_PART = ROWS * F4_ROW;            // 12 float4 per row; 192 / 96 per part
 #pragma unroll
@@ -759,6 +774,13 @@ template <bool TMA, bool AUX, bool LOSS>
 static int fwd_grid_for(int n_tiles) {
     return fwd_split(n_tiles) == 2 ? fwd_grid(raster_fwd_kernel<TMA, AUX, LOSS, 2>, 2 * n_tiles) : fwd_grid(raster_fwd_kernel<TMA, AUX, LOSS, 1>, n_tiles);
 }
+// the row-sharded renderer's variant with exchange stores (one warp per tile)
+static void launch_fwd_exch(const FwdArgs &a, cudaStream_t stream) {
+    auto k = raster_fwd_kernel<true, false, false, 1, true>;
+    const int grid = persistent_grid(k, FW_THREADS, FW_SMEM_EXCH, a.n_tiles, "GI2D_FWD_CTAS_PER_SM");
+    k<<<grid, FW_THREADS, FW_SMEM_EXCH, stream>>>(a.TX, a.W, a.H, a.tile_begin, a.n_tiles, a.tile_bins, a.packed, a.src, a.d_status, a.background,
+                                                    a.out_img, a.final_Ts, a.final_idx, a.out_mc, a.vec_ok, a.la, a.peers);
+}
 template <bool TMA, bool AUX, bool LOSS>
 static void launch_fwd(const FwdArgs &a, cudaStream_t stream) {
     const int grid = fwd_grid_for<TMA, AUX, LOSS>(a.n_tiles);
@@ -816,7 +838,10 @@ int gi2d_raster_sum_fwd_packed_rows_mc(int TX, int TY, int W, int H, int ty_begi
     const float4 *p = reinterpret_cast<const float4 *>(packed);
     const int nt = (ty_end - ty_begin) * TX, first = ty_begin * TX;
     const FwdArgs a{TX, W, H, first, nt, tile_bins, p, src, d_status, background, out_img, final_Ts, final_idx, out_img_mc, vok, LossArgs{}, PeerOut{}};
-    if (final_Ts && final_idx) launch_fwd<true, true, false>(a, stream);
+    if (out_img_mc) {
+        if (final_Ts || final_idx) return GI2D_ERR_INVALID;           // the multicast variant writes the image only
+        launch_fwd_exch(a, stream);
+    } else if (final_Ts && final_idx) launch_fwd<true, true, false>(a, stream);
     else launch_fwd<true, false, false>(a, stream);
     return cuda_status();
 }
@@ -840,7 +865,8 @@ int gi2d_raster_sum_fwd_packed_rows_p2p(int TX, int TY, int W, int H, int ty_beg
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     const FwdArgs a{TX, W, H, ty_begin * TX, (ty_end - ty_begin) * TX, tile_bins, reinterpret_cast<const float4 *>(packed), src, nullptr, nullptr,
                     out_img, nullptr, nullptr, nullptr, vok, LossArgs{}, po};
-    launch_fwd<true, false, false>(a, stream);
+    if (n_peers) launch_fwd_exch(a, stream);
+    else launch_fwd<true, false, false>(a, stream);
     return cuda_status();
 }
 
