@@ -501,7 +501,7 @@ constexpr int BW_WARPS = 8;
 constexpr int BW_THREADS = BW_WARPS * 32;
 struct __align__(16) BwdWarpSmem {
     float4 ring[PIPE_NST][PIPE_CHUNK * 3];        // staged records
-    float v[3][GI2D_TILE_PIX];                    // upstream gradient of the tile, one plane per channel
+    float4 v4[GI2D_TILE_PIX * 3 / 4];             // upstream gradient of the tile, interleaved like the image: [16 rows][16 px][rgb]
     uint16_t pref[PIPE_CHUNK + 2];                // exclusive prefix of the unit counts; [PIPE_CHUNK] = total
     uint8_t rect[PIPE_CHUNK];                     // bx0 | nbx<<2 | by0<<5: the 4x2 pixel blocks a record's rectangle touches
     uint64_t bars[PIPE_NST];
@@ -535,20 +535,18 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
         const int k = q >> ishift;
         const int ty = k / TX, tx = k - ty * TX;
         const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
-        // the tile of upstream gradients, zero outside the image (such pixels then contribute exact zeros)
+        // the tile of upstream gradients in the image's own interleaved layout (a straight copy of 16 rows x 12 float4), zero
+        // outside the image (such pixels then contribute exact zeros)
         if (vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H) {
 #pragma unroll
-            for (int q = 0; q < 6; ++q) {                   // 16 rows x 12 float4
+            for (int q = 0; q < 6; ++q) {
                 const int f = q * 32 + lane, row = f / 12, c4 = f - row * 12;
-                const float4 g4 = __ldg(reinterpret_cast<const float4 *>(v_out + ((size_t)(ty0 + row) * W + tx0) * 3) + c4);
-                const float e[4] = {g4.x, g4.y, g4.z, g4.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int fl = 4 * c4 + j, px = fl / 3, ch = fl - 3 * px;
-                    S.v[ch][row * GI2D_TILE + px] = e[j] * vsc;
-                }
+                float4 g4 = __ldg(reinterpret_cast<const float4 *>(v_out + ((size_t)(ty0 + row) * W + tx0) * 3) + c4);
+                g4.x *= vsc; g4.y *= vsc; g4.z *= vsc; g4.w *= vsc;
+                S.v4[f] = g4;
             }
         } else {
+            float *const sv = reinterpret_cast<float *>(S.v4);
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
                 const int p = q * 32 + lane, j = tx0 + (p & 15), i = ty0 + (p >> 4);
@@ -557,10 +555,10 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                     const size_t pix = (size_t)i * W + j;
                     vr = __ldg(v_out + 3 * pix) * vsc; vg = __ldg(v_out + 3 * pix + 1) * vsc; vb = __ldg(v_out + 3 * pix + 2) * vsc;
                 }
-                S.v[0][p] = vr; S.v[1][p] = vg; S.v[2][p] = vb;
+                sv[3 * p] = vr; sv[3 * p + 1] = vg; sv[3 * p + 2] = vb;
             }
         }
-        // (visibility of S.v to the other lanes: the __syncwarp after the prefix stores below)
+        // (visibility of S.v4 to the other lanes: the __syncwarp after the prefix stores below)
 
         for (int off = pipe.c_first; off < cnt; off += pipe.c_step) {
             const int n = min(PIPE_CHUNK, cnt - off);
@@ -628,8 +626,6 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                     // this lane's share of the record's gradients -> ONE set of global reductions (linear in the sums, so
                     // the shares of the lanes that split a record simply add up in memory like those of other tiles do)
                     auto flush = [&]() {
-                        if (S_x == 0.f && S_y == 0.f && S_xx == 0.f && S_xy == 0.f && S_yy == 0.f && a_r == 0.f && a_g == 0.f && a_b == 0.f && S_m == 0.f)
-                            return;
                         const float nop = -opac, hop = -0.5f * opac;              // v_sigma = -opac * m ; the conic terms carry 0.5 (Q7)
                         const float g_x = nop * fmaf(cx, S_x, cy * S_y), g_y = nop * fmaf(cy, S_x, cz * S_y);   // backward.cu:826-827
                         const float g_cxx = hop * S_xx, g_cxy = hop * S_xy, g_cyy = hop * S_yy;                // :823-825
@@ -673,10 +669,8 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                             const int ly = ly0 + r;
                             const float dy = fsub(y, (float)(ty0 + ly));
                             const float t3 = fmul(dy, fmul(cz, dy));
-                            const float4 vr4 = reinterpret_cast<const float4 *>(S.v[0])[ly * 4 + bx];
-                            const float4 vg4 = reinterpret_cast<const float4 *>(S.v[1])[ly * 4 + bx];
-                            const float4 vb4 = reinterpret_cast<const float4 *>(S.v[2])[ly * 4 + bx];
-                            const float vr[4] = {vr4.x, vr4.y, vr4.z, vr4.w}, vg[4] = {vg4.x, vg4.y, vg4.z, vg4.w}, vb[4] = {vb4.x, vb4.y, vb4.z, vb4.w};
+                            const float4 e0 = S.v4[ly * 12 + bx * 3], e1 = S.v4[ly * 12 + bx * 3 + 1], e2 = S.v4[ly * 12 + bx * 3 + 2];
+                            const float vr[4] = {e0.x, e0.w, e1.z, e2.y}, vg[4] = {e0.y, e1.x, e1.w, e2.z}, vb[4] = {e0.z, e1.y, e2.x, e2.w};
                             float u_m = 0.f, u_x = 0.f;          // this row's sum m and sum m dx (dy is constant over the row)
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
