@@ -754,7 +754,12 @@ def run_b200(args):
         if render_only and not all(torch.equal(h, f.cpu()) for h, f in zip(host_out, frame)):
             raise RuntimeError("in-graph e2e pipeline: a frame that reached the host differs from the rendered one")
         stream_op_pipeline, pipelined = pipelined, pipelined_graph
-    pipelined(Wm_e)
+    # untimed: a GPU that idled through the captures above needs a few tens of milliseconds of work before it runs at speed again
+    # (the same replays take 420 us each right after the idle phase and 343 us once warm)
+    t_w = time.perf_counter()
+    pipelined(max(Wm_e, 8 * U))
+    while time.perf_counter() - t_w < 0.05:
+        pipelined(8 * U)
     barrier()
     t0 = time.perf_counter()
     pipelined(K)
@@ -763,16 +768,17 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_s = e2e_s.item()
-    e2e_gpu_ms = None
+    e2e_gpu_ms = e2e_replay_ms = None
     if e2e_graphs is not None and U > 1:                    # device time of the same replays (no host reads): what the graph itself costs
-        a_ev, b_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(K // U + 1)]
         torch.cuda.synchronize()
-        a_ev.record()
+        evs[0].record()
         for j in range(K // U):
             e2e_graphs[j & 1][0].replay()
-        b_ev.record()
+            evs[j + 1].record()
         torch.cuda.synchronize()
-        e2e_gpu_ms = a_ev.elapsed_time(b_ev) / K
+        e2e_gpu_ms = evs[0].elapsed_time(evs[-1]) / K
+        e2e_replay_ms = [evs[j].elapsed_time(evs[j + 1]) for j in range(min(K // U, 8))]
     stream_op_s = None
     if e2e_graphs is not None:                              # the stream-op pipeline beside it, informational
         t0 = time.perf_counter()
@@ -797,22 +803,24 @@ def run_b200(args):
                    + (("the copies are memcpy nodes of the replayed graph (the H2D of step i+1 on a branch parallel to step i"
                        + (", the D2H of frame i-1 on another)" if render_only else ")"))
                       if e2e_graphs is not None else "the copies are stream operations around the replay (copy stream)"),
-           "serial_value": K / serial_s, "device_ms_per_step_of_the_e2e_graphs": e2e_gpu_ms}
+           "serial_value": K / serial_s, "device_ms_per_step_of_the_e2e_graphs": e2e_gpu_ms,
+           "device_ms_of_the_first_replays": e2e_replay_ms}
     if stream_op_s is not None:
         e2e["stream_op_pipeline_value"] = world * K / stream_op_s
     if not render_only:
         # eager + strict (default mode of the public API, what an unchanged caller gets), informational
         G.set_sync_free(False)
-        for _ in range(3):
+        for _ in range(20):
             step.eager()
         torch.cuda.synchronize()
+        n_eager = max(K, 100)
         t0 = time.perf_counter()
-        for _ in range(min(K, 50)):
+        for _ in range(n_eager):
             stage[0][0].copy_(host_in[0], non_blocking=True)
             torch.div(stage[0][0], 255.0, out=step.gt)
             loss, _ = step.eager()
             loss.item()
-        e2e["eager_strict_iters_per_s"] = min(K, 50) / (time.perf_counter() - t0)
+        e2e["eager_strict_iters_per_s"] = n_eager / (time.perf_counter() - t0)
 
     # ---- the rest of BASELINE.json's metric at this N (render FPS, Kodak imgs/s) and the sharded config (8K decode, strong
     # scaling over the ranks): every rank takes part, rank 0 reports them under `extras`
