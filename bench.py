@@ -665,30 +665,39 @@ def run_b200(args):
     multi_out = [[torch.empty(1, dtype=torch.float32).pin_memory() for _ in range(U)] for _ in range(2)] if U > 1 else None
 
     gt_pair = [step.gt, step.gt.clone()] if not render_only else None     # the unrolled steps read alternating target buffers
+    # four uint8 staging buffers: the H2D of step u+2's target is issued two steps ahead (a slow PCIe link -- 1.18 MB took 130 us
+    # on one of the boxes -- then still hides under two steps of compute), its conversion one step ahead
+    stage4 = [torch.empty_like(stage[0][0]) for _ in range(4)] if not render_only else None
+    h2d_stream, conv_stream = copy_stream, torch.cuda.Stream()
 
     def capture_e2e_multi(which):
-        """Critical path of the replayed graph = the U steps only: the H2D of step u+1's target AND its conversion to fp32 (into
-        the other target buffer) run on a branch beside step u; the D2H of a step's loss runs on a third branch."""
+        """Critical path of the replayed graph = the U steps only.  Step u reads gt_pair[u & 1].  Beside it, on other branches:
+        the H2D of step u+2's 8-bit target into stage4[(u + 2) % 4], the conversion of step u+1's (already arrived) target to
+        fp32 into gt_pair[(u + 1) & 1] once step u-1 no longer reads that buffer, and the D2H of step u-1's loss."""
         g = torch.cuda.CUDAGraph()
         keep = []
         gt0 = step.gt
         with torch.cuda.graph(g):
             cap = torch.cuda.current_stream()
+            h2d_stream.wait_stream(cap)
+            conv_stream.wait_stream(cap)
             for u in range(U):
-                b = u & 1
-                # gt_pair[b] holds step u's target (converted by the previous iteration / replay, or before the first replay)
-                copy_stream.wait_stream(cap)                # step u-1 (reader of gt_pair[1 - b]) is ordered before the conversion below
-                with torch.cuda.stream(copy_stream):
-                    stage[1 - b][0].copy_(host_in[0], non_blocking=True)        # H2D from pinned memory: step u+1's target ...
-                    torch.div(stage[1 - b][0], 255.0, out=gt_pair[1 - b])       # ... and its uint8 -> fp32 conversion, beside step u
-                step.gt = gt_pair[b]
+                with torch.cuda.stream(h2d_stream):         # (its previous reader, the conversion for step u-2, is ordered below)
+                    stage4[(u + 2) % 4].copy_(host_in[0], non_blocking=True)
+                conv_stream.wait_stream(cap)                # step u-1, the reader of gt_pair[(u + 1) & 1], has been issued before this point
+                with torch.cuda.stream(conv_stream):
+                    torch.div(stage4[(u + 1) % 4], 255.0, out=gt_pair[(u + 1) & 1])
+                h2d_stream.wait_stream(conv_stream)         # the next H2D into a staging buffer follows the conversions that read it
+                step.gt = gt_pair[u & 1]
                 k = step.eager()                            # (loss, gradients): stay alive with the graph
                 d2h_stream.wait_stream(cap)
                 with torch.cuda.stream(d2h_stream):
                     multi_out[which][u].copy_(k[0].detach().view(1), non_blocking=True)  # D2H of step u's result, off the critical path
                 keep.append(k)
-                cap.wait_stream(copy_stream)                # step u+1 reads what this branch prepared
+                cap.wait_stream(conv_stream)                # step u+1 reads what the conversion branch prepared
+                conv_stream.wait_stream(h2d_stream)         # ... and the conversion for step u+2 needs its bytes
             cap.wait_stream(d2h_stream)
+            cap.wait_stream(h2d_stream)
         step.gt = gt0
         return g, keep
 
@@ -706,8 +715,9 @@ def run_b200(args):
         if U > 1:                                           # n steps = n / U replays; the host reads every step's result
             assert n % U == 0
             last = 0.0
-            stage[0][0].copy_(host_in[0], non_blocking=True)
-            torch.div(stage[0][0], 255.0, out=gt_pair[0])   # step 0's target; every later one is prepared inside the graphs
+            stage4[0].copy_(host_in[0], non_blocking=True)  # steps 0 and 1: targets brought here; every later one inside the graphs
+            stage4[1].copy_(host_in[0], non_blocking=True)
+            torch.div(stage4[0], 255.0, out=gt_pair[0])
 
             def read(j):
                 ev_done[j & 1].synchronize()
