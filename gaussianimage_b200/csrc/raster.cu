@@ -21,6 +21,7 @@
 // Per-pair arithmetic up to the two comparisons is the reference's instruction sequence (gi2d_common.cuh).
 // FP32-pipe / issue bound; no tensor cores (not a dense contraction).
 #include "gi2d_common.cuh"
+#include <type_traits>
 
 namespace gi2d {
 
@@ -76,6 +77,7 @@ struct ChunkPipe {
     // split the chunk sequence between them (backward: item j takes chunks j, j + c_step, ...; gradients add up in global
     // memory anyway).  The item stride of a warp is a multiple of the items per tile, so c_first is a constant of the warp.
     int tile_begin, n_items, stride, lane, ishift, c_first, c_step;
+    int stage_f4;                                 // float4 per ring stage (>= 3 * PIPE_CHUNK; the forward appends a zero record)
     int pk, p_off;
     int2 p_rg, p_nx;
     uint32_t seq;                                 // chunks consumed so far
@@ -97,12 +99,14 @@ struct ChunkPipe {
         const uint32_t bytes = (uint32_t)min(PIPE_CHUNK, p_rg.y - p_off) * 48u;
         if (lane == 0) {
             mbar_expect_tx(&bars[st], bytes);
-            tma_load_1d(ring + (size_t)st * PIPE_CHUNK * 3, packed + 3 * (size_t)(p_rg.x + p_off), bytes, &bars[st]);
+            tma_load_1d(ring + (size_t)st * stage_f4, packed + 3 * (size_t)(p_rg.x + p_off), bytes, &bars[st]);
         }
         p_off += c_step;
     }
     __device__ __forceinline__ void init(const int *tile_bins, const float4 *packed_, float4 *ring_, uint64_t *bars_, int tile_begin_,
-                                         int n_tiles, int ishift_, bool split_chunks, int first, int stride_, int lane_, bool tma) {
+                                         int n_tiles, int ishift_, bool split_chunks, int first, int stride_, int lane_, bool tma,
+                                         int stage_f4_ = PIPE_CHUNK * 3) {
+        stage_f4 = stage_f4_;
         bins2 = reinterpret_cast<const int2 *>(tile_bins);
         packed = packed_; ring = ring_; bars = bars_;
         tile_begin = tile_begin_; ishift = ishift_; n_items = n_tiles << ishift_; stride = stride_; lane = lane_;
@@ -126,7 +130,7 @@ struct ChunkPipe {
     __device__ __forceinline__ float4 *acquire() {
         const int st = (int)(seq % PIPE_NST);
         mbar_wait(&bars[st], (seq / PIPE_NST) & 1u);
-        return ring + (size_t)st * PIPE_CHUNK * 3;
+        return ring + (size_t)st * stage_f4;
     }
     // every lane has left the stage (the caller has just executed __syncwarp): refill it with the chunk PIPE_NST ahead
     __device__ __forceinline__ void release() {
@@ -198,7 +202,8 @@ struct LossArgs {
 constexpr int FW_WARPS = 8;                       // warps per CTA = independent pipelines per CTA
 constexpr int FW_CHUNK = PIPE_CHUNK;
 constexpr int FW_THREADS = FW_WARPS * 32;
-constexpr size_t FW_RING_BYTES = (size_t)FW_WARPS * PIPE_NST * PIPE_CHUNK * 48;
+constexpr int FW_STAGE_F4 = (PIPE_CHUNK + 1) * 3;  // a stage = 64 records + one all-zero record (what a lane without work evaluates)
+constexpr size_t FW_RING_BYTES = (size_t)FW_WARPS * PIPE_NST * FW_STAGE_F4 * 16;
 constexpr size_t FW_OUT_BYTES = (size_t)FW_WARPS * GI2D_TILE_PIX * 3 * 4;        // one output tile per warp (epilogue staging)
 constexpr size_t FW_SMEM = FW_RING_BYTES + (size_t)FW_WARPS * PIPE_NST * 8;
 constexpr size_t FW_SMEM_EXCH = FW_SMEM + FW_OUT_BYTES;
@@ -230,9 +235,12 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
     const bool none_at_all = d_status && background && __ldg(d_status) == 0;   // rasterize_sum.py:121-129
     const int first = warp * G + blockIdx.x, n_items = n_tiles << ISHIFT;
     ChunkPipe pipe;
-    pipe.init(tile_bins, packed, reinterpret_cast<float4 *>(fw_smem) + (size_t)warp * PIPE_NST * PIPE_CHUNK * 3,
+    float4 *const my_ring = reinterpret_cast<float4 *>(fw_smem) + (size_t)warp * PIPE_NST * FW_STAGE_F4;
+    if (lane < 3 * PIPE_NST) my_ring[(lane / 3) * FW_STAGE_F4 + 3 * PIPE_CHUNK + lane % 3] = make_float4(0.f, 0.f, 0.f, 0.f);   // the zero records
+    __syncwarp();
+    pipe.init(tile_bins, packed, my_ring,
               reinterpret_cast<uint64_t *>(fw_smem + FW_RING_BYTES + (EXCH ? FW_OUT_BYTES : 0)) + warp * PIPE_NST, tile_begin, n_tiles,
-              ISHIFT, false, first, stride, lane, TMA);
+              ISHIFT, false, first, stride, lane, TMA, FW_STAGE_F4);
     float4 *const s_out4 = reinterpret_cast<float4 *>(fw_smem + FW_RING_BYTES) + (size_t)warp * (GI2D_TILE_PIX * 3 / 4);   // EXCH only
     const int part = first & (SPLIT - 1);                 // which half of its tiles this warp renders (constant: stride is even)
 
@@ -272,6 +280,7 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
             }
             // which records of the chunk touch this lane's pixel block: 64-bit mask from 2 x (NBX + NBY = 12) ballots
             uint32_t m[2] = {0u, 0u};
+            bool big = false;                              // a record whose opacity is not <= 1: alpha needs the min(1, .) of forward.cu:601
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if (h == 1 && n <= 32) break;              // sparse tiles (8K decode: ~19 records per tile): one round of ballots
@@ -279,7 +288,12 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                 uint32_t colbits = 0, rowbits = 0;
                 if (t < n) {
                     int lx0, lx1, ly0, ly1;
-                    if (record_rect(rec[3 * t], rec[3 * t + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
+                    const float4 A = rec[3 * t];
+                    const float4 Bq = rec[3 * t + 1];
+                    // ... or whose fields could make sigma NaN (non-finite, or large enough to overflow): min(1, NaN) = 1 there
+                    big = big || !(A.z <= 1.f) || !(fabsf(A.x) < 1e6f) || !(fabsf(A.y) < 1e6f) || !(fabsf(A.w) < 1e18f) ||
+                          !(fabsf(Bq.x) < 1e18f) || !(fabsf(Bq.y) < 1e18f);
+                    if (record_rect(A, rec[3 * t + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
                         const int r0 = max(ly0, row0) - row0, r1 = min(ly1, row0 + ROWS - 1) - row0;
                         if (r0 <= r1) {
                             colbits = (2u << (lx1 >> XSH)) - (1u << (lx0 >> XSH));
@@ -301,41 +315,54 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                 m[h] = myC & myR;
             }
             const int n_it = __reduce_max_sync(0xffffffffu, __popc(m[0]) + __popc(m[1]));
+            const bool any_big = __any_sync(0xffffffffu, big);
             const int idx0 = lo + off;
-            for (int it = 0; it < n_it; ++it) {
-                const bool h0 = m[0] != 0u;
-                uint32_t mm = h0 ? m[0] : m[1];
-                const bool act = mm != 0u;
-                const int t = act ? (__ffs((int)mm) - 1 + (h0 ? 0 : 32)) : 0;
-                mm &= mm - 1u;
-                if (h0) m[0] = mm; else m[1] = mm;
-                const float4 A = rec[3 * t], B = rec[3 * t + 1];
-                const float cb = rec[3 * t + 2].x;
-                float dx[BW], u[BW], w[BW];
-#pragma unroll
-                for (int c = 0; c < BW; ++c) {
-                    dx[c] = fsub(A.x, pxf + (float)c);
-                    u[c] = fmul(A.w, dx[c]);                // cx * dx
-                    w[c] = fmul(B.x, dx[c]);                // cy * dx
-                }
-#pragma unroll
-                for (int r = 0; r < 2; ++r) {
-                    const float dy = fsub(A.y, pyf + (float)r);
-                    const float t3 = fmul(dy, fmul(B.y, dy));                          // dy * (cz * dy)
+            // The walk.  A lane whose mask has run out evaluates the stage's all-zero record (sigma = 0, alpha = 0: rejected by
+            // the alpha test like any invisible pair), so the body needs no "lane active" predicate.  The halved conic terms
+            // are exact (a factor 0.5 commutes with every rounding of eval_sigma), so  ffma(dy, w, ffma(dx, hu, ht3))  is
+            // bit for bit  ffma(dy, w, 0.5 * ffma(dx, u, t3)).  With every opacity of the chunk <= 1 (always, in GaussianImage),
+            // opac * exp(-sigma) <= opac <= 1 for every pair that passes sigma >= 0, and the min(1, .) is dropped.
+            auto walk = [&](auto clamp_tag) {
+                constexpr bool CLAMP1 = decltype(clamp_tag)::value;
+                uint32_t m0 = m[0], m1 = m[1];
+                int base = 0;
+                for (int it = 0; it < n_it; ++it) {
+                    const bool z0 = m0 == 0u;
+                    m0 = z0 ? m1 : m0;
+                    m1 = z0 ? 0u : m1;
+                    base = z0 ? 32 : base;
+                    const int t = m0 != 0u ? __ffs((int)m0) - 1 + base : PIPE_CHUNK;
+                    m0 &= m0 - 1u;
+                    const float4 A = rec[3 * t], B = rec[3 * t + 1];
+                    const float cb = rec[3 * t + 2].x;
+                    const float hcx = fmul(A.w, 0.5f), hcz = fmul(B.y, 0.5f);
+                    float dx[BW], hu[BW], w[BW];
 #pragma unroll
                     for (int c = 0; c < BW; ++c) {
-                        const float qq = ffma(dx[c], u[c], t3);                         // eval_sigma, hoisted
-                        const float sigma = ffma(dy, w[c], fmul(qq, 0.5f));
-                        const float alpha = fminf(fmul(A.z, exp_neg(sigma)), 1.f);
-                        if (act && !(sigma < 0.f) && !(alpha < GI2D_ALPHA_MIN)) {      // forward.cu:602-604
-                            acc[r][c][0] = ffma(alpha, B.z, acc[r][c][0]);             // forward.cu:607-609
-                            acc[r][c][1] = ffma(alpha, B.w, acc[r][c][1]);
-                            acc[r][c][2] = ffma(alpha, cb, acc[r][c][2]);
-                            if (AUX) cur[r][c] = idx0 + t;                              // forward.cu:611
+                        dx[c] = fsub(A.x, pxf + (float)c);
+                        hu[c] = fmul(hcx, dx[c]);               // 0.5 * (cx * dx)
+                        w[c] = fmul(B.x, dx[c]);                // cy * dx
+                    }
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        const float dy = fsub(A.y, pyf + (float)r);
+                        const float ht3 = fmul(dy, fmul(hcz, dy));                         // 0.5 * (dy * (cz * dy))
+#pragma unroll
+                        for (int c = 0; c < BW; ++c) {
+                            const float sigma = ffma(dy, w[c], ffma(dx[c], hu[c], ht3));    // eval_sigma, hoisted
+                            const float ov = fmul(A.z, exp_neg(sigma));
+                            const float alpha = CLAMP1 ? fminf(ov, 1.f) : ov;
+                            if (!(sigma < 0.f) && !(alpha < GI2D_ALPHA_MIN)) {              // forward.cu:602-604
+                                acc[r][c][0] = ffma(alpha, B.z, acc[r][c][0]);             // forward.cu:607-609
+                                acc[r][c][1] = ffma(alpha, B.w, acc[r][c][1]);
+                                acc[r][c][2] = ffma(alpha, cb, acc[r][c][2]);
+                                if (AUX) cur[r][c] = idx0 + t;                              // forward.cu:611
+                            }
                         }
                     }
                 }
-            }
+            };
+            if (any_big) walk(std::true_type{}); else walk(std::false_type{});
             __syncwarp();                                  // every lane has left the stage
             if (TMA) pipe.release();                       // refill it with the chunk PIPE_NST ahead
         }
@@ -572,11 +599,17 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
             // per record: visible rectangle -> the aligned 4x2 pixel blocks it touches = units; warp-wide exclusive scan of the counts
             int units[2], ubeg[2];
             int run = 0;
+            bool big = false;                              // a record whose alpha needs the min(1, .) of backward.cu:805 (see the forward)
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int t = 32 * h + lane;
                 int lx0 = 0, lx1 = 0, ly0 = 0, ly1 = 0, un = 0;
                 uint32_t rect = 0;
+                if (t < n) {
+                    const float4 A = rec[3 * t], Bq = rec[3 * t + 1];
+                    big = big || !(A.z <= 1.f) || !(fabsf(A.x) < 1e6f) || !(fabsf(A.y) < 1e6f) || !(fabsf(A.w) < 1e18f) ||
+                          !(fabsf(Bq.x) < 1e18f) || !(fabsf(Bq.y) < 1e18f);
+                }
                 if (t < n && record_rect(rec[3 * t], rec[3 * t + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
                     const int bx0 = lx0 >> 2, nbx = (lx1 >> 2) - bx0 + 1, by0 = ly0 >> 1, nby = (ly1 >> 1) - by0 + 1;
                     un = nbx * nby;
@@ -596,6 +629,7 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
             }
             const int total = run;
             if (lane == 0) S.pref[PIPE_CHUNK] = (uint16_t)total;
+            const bool any_big = __any_sync(0xffffffffu, big);
             __syncwarp();
             if (total > 0) {
                 // ---- main loop: this lane's contiguous piece of the flattened unit list
@@ -610,92 +644,108 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                         if ((int)S.pref[t + step] <= u) t += step;
                     float S_m = 0.f, S_x = 0.f, S_y = 0.f, S_xx = 0.f, S_xy = 0.f, S_yy = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f;
                     // current record (registers) and its block range
-                    float x, y, opac, cx, cy, cz, cr, cg, cb;
+                    float x, y, opac, hcx, cy, hcz, cr, cg, cb;      // hcx, hcz: HALF the conic's diagonal (0.5 cx dx dx + 0.5 cz dy dy: exact)
                     int bx0, nbx, by0, base, rec_end;
                     size_t gid;
                     auto load_record = [&]() {
                         const float4 A = rec[3 * t], B = rec[3 * t + 1];
                         const float2 C = *reinterpret_cast<const float2 *>(&rec[3 * t + 2]);
                         cb = C.x; gid = (size_t)__float_as_int(C.y);
-                        x = A.x; y = A.y; opac = A.z; cx = A.w; cy = B.x; cz = B.y; cr = B.z; cg = B.w;
+                        x = A.x; y = A.y; opac = A.z; hcx = fmul(A.w, 0.5f); cy = B.x; hcz = fmul(B.y, 0.5f); cr = B.z; cg = B.w;
                         const uint32_t rect = S.rect[t];
                         bx0 = rect & 3; nbx = (rect >> 2) & 7; by0 = rect >> 5;
                         base = (int)S.pref[t];
                         rec_end = (int)S.pref[t + 1];
                     };
-                    // this lane's share of the record's gradients -> ONE set of global reductions (linear in the sums, so
-                    // the shares of the lanes that split a record simply add up in memory like those of other tiles do)
-                    auto flush = [&]() {
-                        const float nop = -opac, hop = -0.5f * opac;              // v_sigma = -opac * m ; the conic terms carry 0.5 (Q7)
-                        const float g_x = nop * fmaf(cx, S_x, cy * S_y), g_y = nop * fmaf(cy, S_x, cz * S_y);   // backward.cu:826-827
-                        const float g_cxx = hop * S_xx, g_cxy = hop * S_xy, g_cyy = hop * S_yy;                // :823-825
-                        if (VEC12) {
-                            float *row = out.g12 + 12 * gid;
-                            red_add_v4(row, g_x, g_y, g_cxx, g_cxy);
-                            red_add_v4(row + 4, g_cyy, a_r, a_g, a_b);
-                            atomicAdd(row + 8, S_m);
-                        } else {
-                            atomicAdd(out.v_xy + 2 * gid, g_x); atomicAdd(out.v_xy + 2 * gid + 1, g_y);
-                            atomicAdd(out.v_conic + 3 * gid, g_cxx); atomicAdd(out.v_conic + 3 * gid + 1, g_cxy); atomicAdd(out.v_conic + 3 * gid + 2, g_cyy);
-                            atomicAdd(out.v_colors + 3 * gid, a_r); atomicAdd(out.v_colors + 3 * gid + 1, a_g); atomicAdd(out.v_colors + 3 * gid + 2, a_b);
-                            atomicAdd(out.v_opacity + gid, S_m);
-                        }
-                    };
-                    load_record();
-                    // ONE flat loop over the piece: crossing into the next record is a short divergent branch (flush, find, load),
-                    // the eight-pixel body stays converged across the warp
-                    for (; u < uend; ++u) {
-                        if (u >= rec_end) {
-                            flush();
-                            S_m = S_x = S_y = S_xx = S_xy = S_yy = a_r = a_g = a_b = 0.f;
-                            do { ++t; } while ((int)S.pref[t + 1] <= u);        // next record that has units
-                            load_record();
-                        }
-                        const int kk = u - base;
-                        const int rowb = nbx == 1 ? kk : nbx == 2 ? (kk >> 1) : nbx == 4 ? (kk >> 2) : ((kk * 43) >> 7);
-                        const int bx = bx0 + kk - rowb * nbx, ly0 = 2 * (by0 + rowb);
-                        const float fx0 = (float)(tx0 + 4 * bx);
-                        float dx[4], cu[4], cw[4];
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            dx[j] = fsub(x, fx0 + (float)j);
-                            cu[j] = fmul(cx, dx[j]);
-                            cw[j] = fmul(cy, dx[j]);
-                        }
-                        // Pixels of the block outside the record's rectangle need no test of their own: the rectangle is a
-                        // conservative bound of where the alpha test can pass, so that test rejects them (as in the forward).
-#pragma unroll
-                        for (int r = 0; r < 2; ++r) {
-                            const int ly = ly0 + r;
-                            const float dy = fsub(y, (float)(ty0 + ly));
-                            const float t3 = fmul(dy, fmul(cz, dy));
-                            const float4 e0 = S.v4[ly * 12 + bx * 3], e1 = S.v4[ly * 12 + bx * 3 + 1], e2 = S.v4[ly * 12 + bx * 3 + 2];
-                            const float vr[4] = {e0.x, e0.w, e1.z, e2.y}, vg[4] = {e0.y, e1.x, e1.w, e2.z}, vb[4] = {e0.z, e1.y, e2.x, e2.w};
-                            float u_m = 0.f, u_x = 0.f;          // this row's sum m and sum m dx (dy is constant over the row)
+                    // One flat loop over the piece; crossing into the next record is a short divergent branch (flush, find, load),
+                    // the eight-pixel body stays converged across the warp.  CLAMP1 = false (every opacity of the chunk <= 1, so
+                    // alpha = opac * vis needs no min): the colour sums run over vis instead of alpha and take the factor opac in
+                    // the flush -- one select per pixel (vis or 0) instead of two.
+                    auto piece = [&](auto clamp_tag) {
+                        constexpr bool CLAMP1 = decltype(clamp_tag)::value;
+                        // this lane's share of the record's gradients -> ONE set of global reductions (linear in the sums, so
+                        // the shares of the lanes that split a record simply add up in memory like those of other tiles do)
+                        auto flush = [&]() {
+                            const float nop = -opac, hop = -0.5f * opac;              // v_sigma = -opac * m ; the conic terms carry 0.5 (Q7)
+                            const float cx = hcx + hcx, cz = hcz + hcz;
+                            const float g_x = nop * fmaf(cx, S_x, cy * S_y), g_y = nop * fmaf(cy, S_x, cz * S_y);   // backward.cu:826-827
+                            const float g_cxx = hop * S_xx, g_cxy = hop * S_xy, g_cyy = hop * S_yy;                // :823-825
+                            const float csc = CLAMP1 ? 1.f : opac;
+                            const float o_r = csc * a_r, o_g = csc * a_g, o_b = csc * a_b;
+                            if (VEC12) {
+                                float *row = out.g12 + 12 * gid;
+                                red_add_v4(row, g_x, g_y, g_cxx, g_cxy);
+                                red_add_v4(row + 4, g_cyy, o_r, o_g, o_b);
+                                atomicAdd(row + 8, S_m);
+                            } else {
+                                atomicAdd(out.v_xy + 2 * gid, g_x); atomicAdd(out.v_xy + 2 * gid + 1, g_y);
+                                atomicAdd(out.v_conic + 3 * gid, g_cxx); atomicAdd(out.v_conic + 3 * gid + 1, g_cxy); atomicAdd(out.v_conic + 3 * gid + 2, g_cyy);
+                                atomicAdd(out.v_colors + 3 * gid, o_r); atomicAdd(out.v_colors + 3 * gid + 1, o_g); atomicAdd(out.v_colors + 3 * gid + 2, o_b);
+                                atomicAdd(out.v_opacity + gid, S_m);
+                            }
+                        };
+                        for (; u < uend; ++u) {
+                            if (u >= rec_end) {
+                                flush();
+                                S_m = S_x = S_y = S_xx = S_xy = S_yy = a_r = a_g = a_b = 0.f;
+                                do { ++t; } while ((int)S.pref[t + 1] <= u);        // next record that has units
+                                load_record();
+                            }
+                            const int kk = u - base;
+                            const int rowb = nbx == 1 ? kk : nbx == 2 ? (kk >> 1) : nbx == 4 ? (kk >> 2) : ((kk * 43) >> 7);
+                            const int bx = bx0 + kk - rowb * nbx, ly0 = 2 * (by0 + rowb);
+                            const float fx0 = (float)(tx0 + 4 * bx);
+                            float dx[4], hu[4], cw[4];
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
-                                const float q = ffma(dx[j], cu[j], t3);
-                                const float sigma = ffma(dy, cw[j], fmul(q, 0.5f));
-                                const float vis = exp_neg(sigma);
-                                const float raw = fminf(fmul(opac, vis), 1.f);
-                                const bool valid = !(sigma < 0.f) && !(raw < GI2D_ALPHA_MIN);                               // backward.cu:806-808
-                                const float alpha = valid ? raw : 0.f;
-                                a_r = fmaf(alpha, vr[j], a_r); a_g = fmaf(alpha, vg[j], a_g); a_b = fmaf(alpha, vb[j], a_b);   // backward.cu:814
-                                const float v_alpha = fmaf(cr, vr[j], fmaf(cg, vg[j], cb * vb[j]));                          // :818-820
-                                const float m = valid ? vis * v_alpha : 0.f;
-                                const float mdx = m * dx[j];
-                                u_m += m;
-                                u_x += mdx;
-                                S_xx = fmaf(mdx, dx[j], S_xx);
+                                dx[j] = fsub(x, fx0 + (float)j);
+                                hu[j] = fmul(hcx, dx[j]);
+                                cw[j] = fmul(cy, dx[j]);
                             }
-                            S_m += u_m; S_x += u_x;
-                            const float mdy = u_m * dy;
-                            S_y += mdy;
-                            S_yy = fmaf(mdy, dy, S_yy);
-                            S_xy = fmaf(u_x, dy, S_xy);
+                            // Pixels of the block outside the record's rectangle need no test of their own: the rectangle is a
+                            // conservative bound of where the alpha test can pass, so that test rejects them (as in the forward).
+#pragma unroll
+                            for (int r = 0; r < 2; ++r) {
+                                const int ly = ly0 + r;
+                                const float dy = fsub(y, (float)(ty0 + ly));
+                                const float ht3 = fmul(dy, fmul(hcz, dy));
+                                const float4 e0 = S.v4[ly * 12 + bx * 3], e1 = S.v4[ly * 12 + bx * 3 + 1], e2 = S.v4[ly * 12 + bx * 3 + 2];
+                                const float vr[4] = {e0.x, e0.w, e1.z, e2.y}, vg[4] = {e0.y, e1.x, e1.w, e2.z}, vb[4] = {e0.z, e1.y, e2.x, e2.w};
+                                float u_m = 0.f, u_x = 0.f;          // this row's sum m and sum m dx (dy is constant over the row)
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    const float sigma = ffma(dy, cw[j], ffma(dx[j], hu[j], ht3));
+                                    const float vis = exp_neg(sigma);
+                                    const float ov = fmul(opac, vis);
+                                    const float raw = CLAMP1 ? fminf(ov, 1.f) : ov;
+                                    const bool valid = !(sigma < 0.f) && !(raw < GI2D_ALPHA_MIN);                               // backward.cu:806-808
+                                    const float v_alpha = fmaf(cr, vr[j], fmaf(cg, vg[j], cb * vb[j]));                          // :818-820
+                                    float m;
+                                    if (CLAMP1) {
+                                        const float alpha = valid ? raw : 0.f;
+                                        a_r = fmaf(alpha, vr[j], a_r); a_g = fmaf(alpha, vg[j], a_g); a_b = fmaf(alpha, vb[j], a_b);   // backward.cu:814
+                                        m = valid ? vis * v_alpha : 0.f;
+                                    } else {
+                                        const float vis0 = valid ? vis : 0.f;
+                                        a_r = fmaf(vis0, vr[j], a_r); a_g = fmaf(vis0, vg[j], a_g); a_b = fmaf(vis0, vb[j], a_b);
+                                        m = vis0 * v_alpha;
+                                    }
+                                    const float mdx = m * dx[j];
+                                    u_m += m;
+                                    u_x += mdx;
+                                    S_xx = fmaf(mdx, dx[j], S_xx);
+                                }
+                                S_m += u_m; S_x += u_x;
+                                const float mdy = u_m * dy;
+                                S_y += mdy;
+                                S_yy = fmaf(mdy, dy, S_yy);
+                                S_xy = fmaf(u_x, dy, S_xy);
+                            }
                         }
-                    }
-                    flush();
+                        flush();
+                    };
+                    load_record();
+                    if (any_big) piece(std::true_type{}); else piece(std::false_type{});
                 }
             }
             __syncwarp();                                  // every lane has left the stage, rect / pref are free again
