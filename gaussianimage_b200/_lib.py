@@ -30,6 +30,7 @@ _SIGNATURES = {
     "gi2d_cov2d_bounds": (_i, [_i, _vp, _vp, _vp, _vp]),
     "gi2d_scan_workspace_bytes": (_sz, [_i]),
     "gi2d_scan_tiles": (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gi2d_scan_tiles_static": (_i, [_i, _vp, _vp, _vp, _vp]),
     "gi2d_emit_isects": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "gi2d_sort_workspace_bytes": (_sz, [_i, _i, _i]),
     "gi2d_sort_isects": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _sz, _vp]),

@@ -42,6 +42,7 @@ const char *gi2d_status_string(int status) {
     if (status == GI2D_OK) return "ok";
     if (status == GI2D_ERR_INVALID) return "invalid argument";
     if (status == GI2D_ERR_WORKSPACE) return "workspace too small";
+    if (status == GI2D_ERR_STATIC_LIMIT) return "size exceeds the library's static scratch (see the limit in include/gi2d.h)";
     if (status >= GI2D_ERR_CUDA_BASE) return cudaGetErrorString((cudaError_t)(status - GI2D_ERR_CUDA_BASE));
     return "unknown status";
 }

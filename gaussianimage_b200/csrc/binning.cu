@@ -1463,4 +1463,54 @@ int gi2d_repack_records(int capacity, const int *gids_sorted, const int *status,
     return gi2d_repack_records_ex(capacity, gids_sorted, status, xys, conics, colors, opacities, packed, 0, nullptr, stream);
 }
 
+// ---- allocation-free variant of gi2d_scan_tiles (no counterpart in the reference; see include/gi2d.h) -----------------
+// The scan's scratch (control block + one look-back word per block of 1024 Gaussians) lives in a file-scope device array,
+// resident on every GPU that loads the library until the process exits: GI2D_SCAN_STATIC_BYTES = 24832 bytes, enough for
+// GI2D_SCAN_STATIC_MAX_N = 2^22 Gaussians.  In host code `g_scan_static` is only a handle: the device address is looked up
+// once per device with cudaGetSymbolAddress (that device current) and cached.  All calls on a device share the array.
+constexpr size_t SCAN_STATIC_CTL_BYTES = (sizeof(uint32_t) * CTL_WORDS + 255) / 256 * 256;
+constexpr size_t SCAN_STATIC_BYTES = SCAN_STATIC_CTL_BYTES + sizeof(uint32_t) * (GI2D_SCAN_STATIC_MAX_N / 1024);
+static_assert(SCAN_STATIC_BYTES == GI2D_SCAN_STATIC_BYTES, "include/gi2d.h states the size of the static scratch");
+static __device__ __align__(256) unsigned char g_scan_static[SCAN_STATIC_BYTES];
+
+static int scan_static_address(void **out) {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static void *addr[MAX_DEV] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return GI2D_ERR_CUDA_BASE + (int)e;
+    if (dev < 0 || dev >= MAX_DEV) return GI2D_ERR_INVALID;
+    std::lock_guard<std::mutex> g(mu);
+    if (!addr[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_scan_static);      // the current device's copy of the array
+        if (e != cudaSuccess) return GI2D_ERR_CUDA_BASE + (int)e;
+        if (!p) return GI2D_ERR_INVALID;
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return GI2D_OK;
+}
+
+int gi2d_scan_tiles_static(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *total_out, cudaStream_t stream) {
+    if (N <= 0 || !num_tiles_hit || !cum_tiles_hit) return GI2D_ERR_INVALID;
+    if (N > GI2D_SCAN_STATIC_MAX_N) return GI2D_ERR_STATIC_LIMIT;
+    void *ws = nullptr;
+    const int rc = scan_static_address(&ws);
+    if (rc != GI2D_OK) return rc;
+    const size_t need = gi2d_scan_workspace_bytes(N);      // <= SCAN_STATIC_BYTES for every accepted N
+    uint32_t *ctl = reinterpret_cast<uint32_t *>(ws);
+    uint32_t *state = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(ws) + SCAN_STATIC_CTL_BYTES);
+    cudaMemsetAsync(ws, 0, need, stream);                  // the array keeps the previous call's flags: everything read starts at zero
+    PassPlan none;
+    none.npass = 0;
+    const int grid = (N + 1023) / 1024;
+    // look-back in ticket order: correct whether or not all blocks are co-resident
+    scan_kernel<false, 1024><<<grid, 1024, 0, stream>>>(N, num_tiles_hit, cum_tiles_hit, ctl, state, nullptr, nullptr, 0, 0, 0, nullptr,
+                                                   nullptr, none, nullptr, 0, nullptr, nullptr, 1, 0, 0, 0x7fffffff);
+    if (total_out) cudaMemcpyAsync(total_out, ctl + CTL_N, sizeof(int), cudaMemcpyDefault, stream);
+    return cuda_status();
+}
+
 }  // extern "C"

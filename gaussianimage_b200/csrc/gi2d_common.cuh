@@ -19,6 +19,9 @@
 #define GI2D_OK 0
 #define GI2D_ERR_INVALID 1
 #define GI2D_ERR_WORKSPACE 2
+#ifndef GI2D_ERR_STATIC_LIMIT
+#define GI2D_ERR_STATIC_LIMIT 3   // size beyond the static scratch of gi2d_scan_tiles_static (include/gi2d.h)
+#endif
 #define GI2D_ERR_CUDA_BASE 1000   // 1000 + cudaError_t
 
 namespace gi2d {

@@ -10,6 +10,7 @@
  *   0                       success (launch accepted)
  *   GI2D_ERR_INVALID   (1)  invalid argument
  *   GI2D_ERR_WORKSPACE (2)  workspace too small
+ *   GI2D_ERR_STATIC_LIMIT (3)  size beyond what the library's static scratch holds (only gi2d_scan_tiles_static)
  *   1000 + cudaError_t      CUDA launch error
  * Tiles are 16x16 pixels (reference config.h:1-4; helpers.cuh:36-41 hard-codes 16, quirk Q3):
  * TX = ceil(W/16), TY = ceil(H/16).  Layouts are the reference's: (N,2)/(N,3) fp32 row-major, images (H,W,3) fp32,
@@ -33,6 +34,9 @@ typedef struct CUstream_st *cudaStream_t;
 #define GI2D_ABI_VERSION 2
 #define GI2D_ERR_INVALID 1
 #define GI2D_ERR_WORKSPACE 2
+#ifndef GI2D_ERR_STATIC_LIMIT
+#define GI2D_ERR_STATIC_LIMIT 3 /* problem larger than the library's static scratch (gi2d_scan_tiles_static) */
+#endif
 #define GI2D_ERR_CUDA_BASE 1000
 
 int gi2d_abi_version(void);
@@ -111,6 +115,18 @@ int gi2d_cov2d_bounds(int N, const float *cov2d, float *conics, float *radii, cu
 size_t gi2d_scan_workspace_bytes(int N);
 int gi2d_scan_tiles(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *total_out, void *ws, size_t ws_bytes,
                     cudaStream_t stream);
+
+/* gi2d_scan_tiles WITHOUT a workspace argument and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid it).  Same kernel, same results as gi2d_scan_tiles; the scratch is a file-scope device array
+ * of GI2D_SCAN_STATIC_BYTES bytes inside the library, held by every GPU that loads it until the process exits.
+ * Limit: N <= GI2D_SCAN_STATIC_MAX_N, beyond it GI2D_ERR_STATIC_LIMIT is returned and nothing is launched.  The call makes
+ * no cudaMalloc / cudaFree and calls no allocating library routine (one async memset of the scratch, one kernel, one
+ * 4-byte async copy when total_out is given).  ALL calls on a device share the one array: calls that overlap on the GPU
+ * (different streams, or graphs replayed concurrently) race -- serialise them, or use gi2d_scan_tiles with own workspaces. */
+#define GI2D_SCAN_STATIC_MAX_N (1 << 22)
+#define GI2D_SCAN_STATIC_BYTES 24832
+int gi2d_scan_tiles_static(int N, const int *num_tiles_hit, int *cum_tiles_hit, int *total_out, cudaStream_t stream);
 
 /* Replaces map_gaussian_to_intersects (ext.cpp:13 -> bindings.cu:274-313 -> forward.cu:100-136).
  * isect_ids (n_isect) int64, gaussian_ids (n_isect) int32. */

@@ -17,7 +17,7 @@ def declared():
 def test_header_declares_the_hot_path_entry_points():
     names = declared()
     for must in ("gi2d_project_cholesky_fwd", "gi2d_project_cholesky_bwd", "gi2d_project_scale_rot_fwd", "gi2d_project_scale_rot_bwd",
-                 "gi2d_cov2d_bounds", "gi2d_scan_tiles", "gi2d_emit_isects", "gi2d_sort_isects", "gi2d_tile_bins", "gi2d_bin_fused",
+                 "gi2d_cov2d_bounds", "gi2d_scan_tiles", "gi2d_scan_tiles_static", "gi2d_emit_isects", "gi2d_sort_isects", "gi2d_tile_bins", "gi2d_bin_fused",
                  "gi2d_raster_sum_fwd", "gi2d_raster_sum_bwd", "gi2d_raster_sum_fwd_packed", "gi2d_raster_sum_bwd_packed"):
         assert must in names
 
