@@ -25,6 +25,24 @@
 
 namespace gi2d {
 
+// -DGI2D_TRACE (tools/trace_raster.py builds its own copy of the library with it; never the product build): every warp of the
+// rasterizers writes {globaltimer at entry, clock at entry, clock after its first chunk landed, clock at exit, SM id, records}
+// to a buffer, to see launch ramp, load latency and tail separately.
+#ifdef GI2D_TRACE
+__device__ unsigned long long *g_trace = nullptr;
+#define GI2D_TRACE_DECL unsigned long long tr_[6] = {0, 0, 0, 0, 0, 0}
+#define GI2D_TRACE_ENTRY do { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr_[0])); tr_[1] = clock64(); unsigned sm_; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_)); tr_[4] = sm_; } while (0)
+#define GI2D_TRACE_FIRST do { if (!tr_[2]) tr_[2] = clock64(); } while (0)
+#define GI2D_TRACE_WORK(n) do { tr_[5] += (n); } while (0)
+#define GI2D_TRACE_EXIT(widx) do { tr_[3] = clock64(); if (g_trace && (threadIdx.x & 31) == 0) for (int k_ = 0; k_ < 6; ++k_) g_trace[6 * (size_t)(widx) + k_] = tr_[k_]; } while (0)
+#else
+#define GI2D_TRACE_DECL
+#define GI2D_TRACE_ENTRY
+#define GI2D_TRACE_FIRST
+#define GI2D_TRACE_WORK(n)
+#define GI2D_TRACE_EXIT(widx)
+#endif
+
 struct GatherSrc {        // index-indirect sources of the reference-typed entry points
     const int *gids_sorted;
     const float *xys, *conics, *colors, *opac;
@@ -223,6 +241,8 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                                                                 float *__restrict__ final_Ts, int *__restrict__ final_idx,
                                                                 float *out_mc, int vec_ok, LossArgs la = LossArgs{},
                                                                 PeerOut peers = PeerOut{}) {
+    GI2D_TRACE_DECL;
+    GI2D_TRACE_ENTRY;
     constexpr int ISHIFT = SPLIT == 2 ? 1 : 0;
     constexpr int BW = 4 / SPLIT;                         // pixels per lane and row
     constexpr int XSH = SPLIT == 2 ? 1 : 2;               // log2(BW)
@@ -278,6 +298,8 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                 rec = pipe.ring;
                 gather_chunk(rec, src, lo + off, n, lane);
             }
+            GI2D_TRACE_FIRST;
+            GI2D_TRACE_WORK(n);
             // which records of the chunk touch this lane's pixel block: 64-bit mask from 2 x (NBX + NBY = 12) ballots
             uint32_t m[2] = {0u, 0u};
             bool big = false;                              // a record whose opacity is not <= 1: alpha needs the min(1, .) of forward.cu:601
@@ -467,6 +489,7 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
             __syncwarp();                                  // the staging tile is free for the next tile
         }
     }
+    GI2D_TRACE_EXIT(blockIdx.x * FW_WARPS + warp);
     if (LOSS) {
         __shared__ float s_red[FW_WARPS];
         __shared__ bool s_last;
@@ -543,6 +566,8 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                                                                 const float4 *__restrict__ packed, GatherSrc src,
                                                                 const float *__restrict__ v_out, GradOut out, int vec_ok,
                                                                 const float *__restrict__ v_scale = nullptr) {
+    GI2D_TRACE_DECL;
+    GI2D_TRACE_ENTRY;
     extern __shared__ __align__(128) unsigned char bw_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     BwdWarpSmem &S = reinterpret_cast<BwdWarpSmem *>(bw_smem)[warp];
@@ -596,6 +621,8 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                 rec = pipe.ring;
                 gather_chunk(rec, src, lo + off, n, lane);
             }
+            GI2D_TRACE_FIRST;
+            GI2D_TRACE_WORK(n);
             // per record: visible rectangle -> the aligned 4x2 pixel blocks it touches = units; warp-wide exclusive scan of the counts
             int units[2], ubeg[2];
             int run = 0;
@@ -752,6 +779,7 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
             if (TMA) pipe.release();
         }
     }
+    GI2D_TRACE_EXIT(blockIdx.x * BW_WARPS + warp);
 }
 
 static inline int cuda_status() {
@@ -1016,3 +1044,9 @@ int gi2d_raster_sum_bwd_packed_scaled(int N, int TX, int TY, int W, int H, const
 }
 
 }  // extern "C"
+
+#ifdef GI2D_TRACE
+extern "C" int gi2d_debug_set_trace(void *buf) {
+    return (int)cudaMemcpyToSymbol(gi2d::g_trace, &buf, sizeof(buf));
+}
+#endif

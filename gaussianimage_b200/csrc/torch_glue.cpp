@@ -6,11 +6,14 @@
 // device code and no arithmetic.  Two layers:
 //   * plain "check inputs, allocate outputs, launch" calls (project_fwd, fused_forward, raster_bwd_packed, ...) used by the
 //     Python autograd Functions (GI2D_CPP_AUTOGRAD=0);
-//   * the two operators as torch::autograd::Function (ProjectFn, RasterFn) together with the whole policy of the fused
+//   * the two operators as autograd nodes (ProjectNode, RasterNode) together with the whole policy of the fused
 //     chain -- which tensors are known to come from one of our projections, workspace sizing, memoised binning, overflow
 //     bookkeeping -- so that one operator call is one Python -> C++ transition (default when this module is built).
 // When the module is absent the ctypes path of cuda.py runs (GI2D_HOST_GLUE=0 forces it).
 #include <torch/extension.h>
+#include <torch/csrc/autograd/function.h>
+#include <torch/csrc/autograd/functions/utils.h>
+#include <torch/csrc/autograd/saved_variable.h>
 #include <c10/cuda/CUDAGuard.h>
 #include <c10/cuda/CUDAStream.h>
 #include <cuda_runtime_api.h>
@@ -272,7 +275,6 @@ inline int64_t default_capacity(int64_t N) { return std::max<int64_t>(4 * N, 1 <
 // ---------------------------------------------------------------------------------------------------------------------
 // The two operators as torch::autograd::Function
 // ---------------------------------------------------------------------------------------------------------------------
-using torch::autograd::AutogradContext;
 using torch::autograd::variable_list;
 
 inline bool packed_pair(const Tensor &v_xy, const Tensor &v_conic) {   // cuda.py: _is_packed_pair
@@ -284,60 +286,58 @@ inline bool packed_pair(const Tensor &v_xy, const Tensor &v_conic) {   // cuda.p
          reinterpret_cast<uintptr_t>(v_xy.data_ptr()) % 16 == 0;
 }
 
-// project_gaussians_2d.py / project_gaussians_2d_scale_rot.py: _ProjectGaussians2d[ScaleRot]
-struct ProjectFn : public torch::autograd::Function<ProjectFn> {
-  static variable_list forward(AutogradContext *ctx, const Tensor &means2d, const Tensor &p0, const Tensor &p1, int64_t mode,
-                               int64_t H, int64_t W, int64_t TX, int64_t TY, int64_t total_host) {
-    const int64_t N = means2d.size(-2);
-    auto out = project_fwd_impl(mode, N, means2d, p0, mode != 0 ? OptTensor(p1) : OptTensor(), H, W, TX, TY,
-                                reinterpret_cast<int *>(total_host));
-    Tensor xys = std::get<0>(out), depths = std::get<1>(out), radii = std::get<2>(out), conics = std::get<3>(out),
-           nth = std::get<4>(out);
-    ctx->saved_data["mode"] = mode;
-    ctx->saved_data["N"] = N;
-    ctx->saved_data["H"] = H;
-    ctx->saved_data["W"] = W;
-    ctx->save_for_backward({p0, p1, radii, conics});
-    ctx->mark_non_differentiable({radii, nth});
-    ctx->set_materialize_grads(false);
-    return {xys, depths, radii, conics, nth};
+// project_gaussians_2d.py / project_gaussians_2d_scale_rot.py: _ProjectGaussians2d[ScaleRot].  A hand-written autograd Node
+// (what torch's generated VariableType code does) rather than torch::autograd::Function: Function::apply spends ~10 us per
+// call on its generic bookkeeping (AutogradContext, output wrapping, dirty / non-differentiable sets), a third of this
+// operator's host time.  Inputs with edges: means2d, p0 [, p1]; outputs with history: xys (0), depths (1), conics (2).
+struct ProjectNode : public torch::autograd::Node {
+  torch::autograd::SavedVariable p0, p1, conics;      // conics is an OUTPUT of this node (saved without its grad_fn: no cycle)
+  Tensor radii;
+  int64_t mode = 0, N = 0, H = 0, W = 0;
+  std::string name() const override { return mode == 0 ? "ProjectGaussians2dBackward" : "ProjectGaussians2dScaleRotBackward"; }
+  void release_variables() override {
+    std::lock_guard<std::mutex> lock(mutex_);
+    p0.reset_data(); p1.reset_data(); conics.reset_data();
+    radii.reset();
   }
-
-  static variable_list backward(AutogradContext *ctx, variable_list g) {
-    const auto saved = ctx->get_saved_variables();
-    const Tensor &p0 = saved[0], &p1 = saved[1], &radii = saved[2], &conics = saved[3];
-    const int64_t mode = ctx->saved_data["mode"].toInt(), N = ctx->saved_data["N"].toInt();
-    const int64_t H = ctx->saved_data["H"].toInt(), W = ctx->saved_data["W"].toInt();
-    Tensor v_xy = g[0], v_conic = g[3];
+  variable_list apply(variable_list &&g) override {
+    std::lock_guard<std::mutex> lock(mutex_);
+    TORCH_CHECK(radii.defined(), "project_gaussians_2d: backward through the graph a second time (saved tensors were freed); "
+                "specify retain_graph=True");
+    const Tensor p0v = p0.unpack(), conv = conics.unpack(shared_from_this());
+    Tensor p1v;
+    if (mode != 0) p1v = p1.unpack();
+    Tensor v_xy = g[0], v_conic = g[2];
     Tensor v_mean2d, v_a, v_b;
     if (packed_pair(v_xy, v_conic)) {
-      auto r = project_bwd_packed(mode, N, p0, mode != 0 ? OptTensor(p1) : OptTensor(), H, W, radii, conics, v_xy);
+      auto r = project_bwd_packed(mode, N, p0v, mode != 0 ? OptTensor(p1v) : OptTensor(), H, W, radii, conv, v_xy);
       v_mean2d = std::get<0>(r);
       v_a = std::get<1>(r);
       if (std::get<2>(r).has_value()) v_b = *std::get<2>(r);
     } else {                                       // cuda.py: project_gaussians_2d[_scale_rot]_backward without v_cov2d
-      c10::cuda::CUDAGuard guard(conics.device());
-      auto f = conics.options().requires_grad(false);
+      c10::cuda::CUDAGuard guard(conv.device());
+      auto f = conv.options().requires_grad(false);
       v_xy = v_xy.defined() ? v_xy.contiguous() : at::zeros({N, 2}, f);
       v_conic = v_conic.defined() ? v_conic.contiguous() : at::zeros({N, 3}, f);
       chk_in(v_xy, "v_xy", at::kFloat);
       chk_in(v_conic, "v_conic", at::kFloat);
       v_mean2d = at::empty({N, 2}, f);
-      cudaStream_t st = stream_of(conics);
+      cudaStream_t st = stream_of(conv);
       if (mode == 0) {
         v_a = at::empty({N, 3}, f);
-        chk(gi2d_project_cholesky_bwd((int)N, fp(p0), (int)H, (int)W, ip(radii), fp(conics), fp(v_xy), fp(v_conic), nullptr,
+        chk(gi2d_project_cholesky_bwd((int)N, fp(p0v), (int)H, (int)W, ip(radii), fp(conv), fp(v_xy), fp(v_conic), nullptr,
                                       v_mean2d.data_ptr<float>(), v_a.data_ptr<float>(), st),
             "project_gaussians_2d_backward");
       } else {
         v_a = at::empty({N, 2}, f);
         v_b = at::empty({N, 1}, f);
-        chk(gi2d_project_scale_rot_bwd((int)N, fp(p0), fp(p1), (int)H, (int)W, ip(radii), fp(conics), fp(v_xy), fp(v_conic),
+        chk(gi2d_project_scale_rot_bwd((int)N, fp(p0v), fp(p1v), (int)H, (int)W, ip(radii), fp(conv), fp(v_xy), fp(v_conic),
                                        nullptr, v_mean2d.data_ptr<float>(), v_a.data_ptr<float>(), v_b.data_ptr<float>(), st),
             "project_gaussians_2d_scale_rot_backward");
       }
     }
-    return {v_mean2d, v_a, v_b, Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
+    if (mode != 0) return {v_mean2d, v_a, v_b};
+    return {v_mean2d, v_a};
   }
 };
 
@@ -356,9 +356,29 @@ variable_list project_autograd(int64_t mode, const Tensor &means2d, const Tensor
     s.ring.p[slot] = -1;
     host = reinterpret_cast<int64_t>(const_cast<int *>(s.ring.p + slot));
   }
-  // Function::apply wants defined tensors: in Cholesky mode the unused third slot carries p0 again (its gradient slot
-  // stays undefined)
-  variable_list out = ProjectFn::apply(means2d, p0, p1.has_value() ? *p1 : p0, mode, H, W, TX, TY, host);
+  const int64_t N = means2d.size(-2);
+  std::shared_ptr<ProjectNode> node;
+  if (mode != 0 ? torch::autograd::compute_requires_grad(means2d, p0, *p1) : torch::autograd::compute_requires_grad(means2d, p0)) {
+    node = std::shared_ptr<ProjectNode>(new ProjectNode(), torch::autograd::deleteNode);
+    node->set_next_edges(mode != 0 ? torch::autograd::collect_next_edges(means2d, p0, *p1)
+                                   : torch::autograd::collect_next_edges(means2d, p0));
+  }
+  variable_list out;
+  {
+    at::AutoDispatchBelowADInplaceOrView below_autograd;
+    auto r = project_fwd_impl(mode, N, means2d, p0, p1, H, W, TX, TY, reinterpret_cast<int *>(host));
+    out = {std::get<0>(r), std::get<1>(r), std::get<2>(r), std::get<3>(r), std::get<4>(r)};   // xys, depths, radii, conics, num_tiles_hit
+  }
+  if (node) {
+    node->mode = mode; node->N = N; node->H = H; node->W = W;
+    node->p0 = torch::autograd::SavedVariable(p0, false);
+    if (mode != 0) node->p1 = torch::autograd::SavedVariable(*p1, false);
+    node->radii = out[2];
+    torch::autograd::set_history(out[0], node);
+    torch::autograd::set_history(out[1], node);
+    torch::autograd::set_history(out[3], node);
+    node->conics = torch::autograd::SavedVariable(out[3], true);
+  }
   {
     std::lock_guard<std::mutex> g(s.mu);
     Projection &e = s.projections[s.proj_next];
@@ -394,16 +414,65 @@ int find_projection(State &s, const Tensor &xys, const Tensor &depths, const Ten
   return -1;
 }
 
-// rasterize_sum.py: _RasterizeGaussiansSum, fused branch.  memo != 0: re-rasterize a memoised binning with other conics /
-// colours / opacities (gi2d_repack_records_ex) instead of running the chain.
-struct RasterFn : public torch::autograd::Function<RasterFn> {
-  static variable_list forward(AutogradContext *ctx, const Tensor &xys, const Tensor &radii, const Tensor &conics,
-                               const Tensor &nth, const Tensor &colors, const Tensor &opacity, const Tensor &background, int64_t H,
-                               int64_t W, int64_t cap, int64_t sticky, bool want_aux, bool want_grads, int64_t memo, int64_t chain_out) {
-    Chain c;
-    const int64_t N = xys.size(0);
+// rasterize_sum.py: _RasterizeGaussiansSum, fused branch, as a hand-written autograd Node (see ProjectNode).  Inputs with
+// edges: xys, conics, colors, opacity; output with history: out_img.
+struct RasterNode : public torch::autograd::Node {
+  Tensor tile_bins, packed, grads12;             // internal tensors of the forward's chain (no autograd history of their own)
+  int64_t N = 0, H = 0, W = 0;
+  std::vector<int64_t> opacity_shape;
+  bool fresh_grads = false;                      // grads12 was zero-filled by the forward's binning chain and not used yet
+  std::string name() const override { return "RasterizeGaussiansSumBackward"; }
+  void release_variables() override {
+    std::lock_guard<std::mutex> lock(mutex_);
+    tile_bins.reset(); packed.reset(); grads12.reset();
+  }
+  variable_list apply(variable_list &&g) override {
+    std::lock_guard<std::mutex> lock(mutex_);
+    variable_list out(4);
+    if (!g[0].defined()) return out;              // only out_alpha was used downstream (the reference ignores v_out_alpha, Q7)
+    TORCH_CHECK(packed.defined(), "rasterize_gaussians_sum: backward through the graph a second time (saved tensors were "
+                "freed); specify retain_graph=True");
+    Tensor v_out = g[0].contiguous();
+    Tensor grads;
+    if (fresh_grads && grads12.defined()) {
+      // the rows were zero-filled by the forward's binning chain: no memset in front of the kernel.  One use only -- a
+      // second backward through the same node (retain_graph) takes the allocating path below.
+      fresh_grads = false;
+      grads = grads12;
+      grads12.reset();
+      chk_in(v_out, "v_out_img", at::kFloat);
+      const int TX = (int)((W + 15) / 16), TY = (int)((H + 15) / 16);
+      c10::cuda::CUDAGuard guard(grads.device());
+      chk(gi2d_raster_sum_bwd_packed_acc((int)N, TX, TY, (int)W, (int)H, ip(tile_bins), fp(packed), fp(v_out), nullptr,
+                                         grads.data_ptr<float>(), stream_of(grads)),
+          "rasterize_sum_backward");
+    } else {
+      grads = raster_bwd_packed(N, H, W, tile_bins, packed, v_out);
+    }
+    out[0] = grads.slice(1, 0, 2);                                    // v_xy
+    out[1] = grads.slice(1, 2, 5);                                    // v_conic
+    out[2] = grads.slice(1, 5, 8);                                    // v_colors
+    out[3] = grads.slice(1, 8, 9).reshape(opacity_shape);             // v_opacity
+    return out;
+  }
+};
+
+// One forward pass.  memo != null: re-rasterize a memoised binning with other conics / colours / opacities
+// (gi2d_repack_records_ex) instead of running the chain.  Returns {out_img, final_Ts (or an undefined tensor)}.
+variable_list raster_apply(const Tensor &xys, const Tensor &radii, const Tensor &conics, const Tensor &nth, const Tensor &colors,
+                           const Tensor &opacity, const Tensor &background, int64_t H, int64_t W, int64_t cap, int64_t sticky,
+                           bool want_aux, bool want_grads, const Memo *memo, Chain *chain_out) {
+  Chain c;
+  const int64_t N = xys.size(0);
+  std::shared_ptr<RasterNode> node;
+  if (want_grads) {
+    node = std::shared_ptr<RasterNode>(new RasterNode(), torch::autograd::deleteNode);
+    node->set_next_edges(torch::autograd::collect_next_edges(xys, conics, colors, opacity));
+  }
+  {
+    at::AutoDispatchBelowADInplaceOrView below_autograd;
     if (memo) {
-      const Memo &m = *reinterpret_cast<const Memo *>(memo);
+      const Memo &m = *memo;
       chk_in(conics, "conics", at::kFloat);
       chk_in(colors, "colors", at::kFloat);
       chk_in(opacity, "opacity", at::kFloat);
@@ -435,48 +504,17 @@ struct RasterFn : public torch::autograd::Function<RasterFn> {
       c = run_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, nullptr, reinterpret_cast<int *>(sticky), want_aux,
                     want_grads);
     }
-    if (chain_out) *reinterpret_cast<Chain *>(chain_out) = c;      // bookkeeping for the caller (memo, last status)
-    ctx->saved_data["N"] = N;
-    ctx->saved_data["H"] = H;
-    ctx->saved_data["W"] = W;
-    ctx->saved_data["opacity_shape"] = opacity.sizes().vec();
-    ctx->saved_data["fresh_grads"] = want_grads;
-    if (want_grads) ctx->save_for_backward({c.tile_bins, c.packed, c.grads12});
-    else ctx->save_for_backward({c.tile_bins, c.packed});
-    Tensor final_Ts = want_aux ? c.final_Ts : at::empty({0}, c.out_img.options());
-    ctx->mark_non_differentiable({final_Ts});
-    ctx->set_materialize_grads(false);
-    return {c.out_img, final_Ts};
   }
-
-  static variable_list backward(AutogradContext *ctx, variable_list g) {
-    variable_list out(15);
-    if (!g[0].defined()) return out;              // only out_alpha was used downstream (the reference ignores v_out_alpha, Q7)
-    const auto saved = ctx->get_saved_variables();
-    const int64_t N = ctx->saved_data["N"].toInt(), H = ctx->saved_data["H"].toInt(), W = ctx->saved_data["W"].toInt();
-    Tensor v_out = g[0].contiguous();
-    Tensor grads;
-    if (ctx->saved_data["fresh_grads"].toBool() && saved.size() == 3) {
-      // the rows were zero-filled by the forward's binning chain: no memset in front of the kernel.  One use only -- a
-      // second backward through the same node (retain_graph) takes the allocating path below.
-      ctx->saved_data["fresh_grads"] = false;
-      grads = saved[2];
-      chk_in(v_out, "v_out_img", at::kFloat);
-      const int TX = (int)((W + 15) / 16), TY = (int)((H + 15) / 16);
-      c10::cuda::CUDAGuard guard(grads.device());
-      chk(gi2d_raster_sum_bwd_packed_acc((int)N, TX, TY, (int)W, (int)H, ip(saved[0]), fp(saved[1]), fp(v_out), nullptr,
-                                         grads.data_ptr<float>(), stream_of(grads)),
-          "rasterize_sum_backward");
-    } else {
-      grads = raster_bwd_packed(N, H, W, saved[0], saved[1], v_out);
-    }
-    out[0] = grads.slice(1, 0, 2);                                                     // v_xy
-    out[2] = grads.slice(1, 2, 5);                                                     // v_conic
-    out[4] = grads.slice(1, 5, 8);                                                     // v_colors
-    out[5] = grads.slice(1, 8, 9).reshape(ctx->saved_data["opacity_shape"].toIntVector());   // v_opacity
-    return out;
+  if (chain_out) *chain_out = c;                  // bookkeeping for the caller (memo, last status)
+  if (node) {
+    node->N = N; node->H = H; node->W = W;
+    node->opacity_shape = opacity.sizes().vec();
+    node->tile_bins = c.tile_bins; node->packed = c.packed; node->grads12 = c.grads12;
+    node->fresh_grads = true;
+    torch::autograd::set_history(c.out_img, node);
   }
-};
+  return {c.out_img, want_aux ? c.final_Ts : Tensor()};
+}
 
 // rasterize_gaussians_sum, fused path, as ONE call: returns {} when the arguments are not the unmodified outputs of one of our
 // projections (the caller then takes the reference's staged sequence), else {out_img} or {out_img, out_alpha}.
@@ -586,15 +624,14 @@ std::vector<Tensor> rasterize(const Tensor &xys, const Tensor &depths, const Ten
   const bool want_grads = at::GradMode::is_enabled() &&
                           (xys.requires_grad() || conics.requires_grad() || colors.requires_grad() || opacity.requires_grad());
   Chain chain;
-  variable_list out = RasterFn::apply(xys, radii, conics, nth, colors, opacity, background, H, W, cap, sticky, return_alpha, want_grads,
-                                      reinterpret_cast<int64_t>(hit), reinterpret_cast<int64_t>(&chain));
+  variable_list out = raster_apply(xys, radii, conics, nth, colors, opacity, background, H, W, cap, sticky, return_alpha, want_grads, hit,
+                                   &chain);
   if (optimistic) {
     const int64_t n = await_total();
     learn(n, true);
     if (n > cap) {                                     // truncated: redo with the exact size (the first pass is dropped)
       cap = exact_cap(n);
-      out = RasterFn::apply(xys, radii, conics, nth, colors, opacity, background, H, W, cap, sticky, return_alpha, want_grads,
-                            reinterpret_cast<int64_t>(hit), reinterpret_cast<int64_t>(&chain));
+      out = raster_apply(xys, radii, conics, nth, colors, opacity, background, H, W, cap, sticky, return_alpha, want_grads, hit, &chain);
     }
   }
   {

@@ -61,3 +61,35 @@ pr.disable()
 torch.cuda.synchronize()
 st = pstats.Stats(pr)
 st.sort_stats("tottime").print_stats(28)
+
+# ---- where a fit step's host time goes, call by call (sync-free, so no call waits for the GPU) -------------------------
+import collections
+
+acc = collections.OrderedDict((k, 0.0) for k in ("project", "rasterize", "mse_loss", "autograd.grad"))
+for _ in range(20):
+    step()
+torch.cuda.synchronize()
+for _ in range(steps):
+    t0 = time.perf_counter()
+    xys, depths, radii, conics, nth = G.project_gaussians_2d(means, L, s.H, s.W, s.tile_bounds)
+    t1 = time.perf_counter()
+    out = G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, colors, d.opacity, s.H, s.W)
+    t2 = time.perf_counter()
+    loss = torch.nn.functional.mse_loss(out, d.gt)
+    t3 = time.perf_counter()
+    torch.autograd.grad(loss, [means, L, colors])
+    t4 = time.perf_counter()
+    acc["project"] += t1 - t0; acc["rasterize"] += t2 - t1; acc["mse_loss"] += t3 - t2; acc["autograd.grad"] += t4 - t3
+torch.cuda.synchronize()
+print("per call, us/step:", {k: round(1e6 * v / steps, 1) for k, v in acc.items()}, "sum", round(1e6 * sum(acc.values()) / steps, 1))
+
+# the autograd engine's nodes on the CPU side (torch.profiler; its own overhead inflates every entry, read the shares)
+try:
+    from torch.profiler import ProfilerActivity, profile
+    with profile(activities=[ProfilerActivity.CPU]) as prof:
+        for _ in range(50):
+            step()
+        torch.cuda.synchronize()
+    print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=30, max_name_column_width=70))
+except Exception as e:  # noqa: BLE001
+    print("torch.profiler unavailable:", e)
