@@ -170,7 +170,11 @@ def run_reference(args):
     line = {"impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_string(name, param, args.workload, W, H, N), "host_threads": cores},
+            # the config block of the GPU arm, key for key (the driver compares the two arms' configs); what is specific to this
+            # arm -- the host threads -- is in cpu_baseline.cores
+            "config": {"workload": workload_string(name, param, args.workload, W, H, N),
+                       "l2": "256 MiB buffer rewritten between timed steps (flush)",
+                       "parallelism": f"image-parallel x{args.gpus}, no collective", "peaks": measured_peaks()[1]},
             "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port",
                              "sample": f"{steps} full {args.workload} steps of {name} (oracle/gi2d_oracle.c, OpenMP)"},
             "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}

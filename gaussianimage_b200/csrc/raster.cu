@@ -91,12 +91,13 @@ struct ChunkPipe {
     float4 *ring;
     uint64_t *bars;
     // Work ITEMS: a tile is 1 << ishift items, dealt to different warps.  Either every item of a tile takes all of the
-    // tile's chunks (forward: the items are the two halves of the tile's pixels; c_first = 0, c_step = 1 chunk) or the items
-    // split the chunk sequence between them (backward: item j takes chunks j, j + c_step, ...; gradients add up in global
-    // memory anyway).  The item stride of a warp is a multiple of the items per tile, so c_first is a constant of the warp.
-    int tile_begin, n_items, stride, lane, ishift, c_first, c_step;
+    // tile's chunks (forward: the items are the two halves of the tile's pixels) or the items
+    // split the chunk sequence between them (backward: item j takes chunks j, j + items, ...; gradients add up in global
+    // memory anyway).  The item stride of a warp is a multiple of the items per tile, so j (jidx) is a constant of the warp.
+    int tile_begin, n_items, stride, lane, ishift;
+    int sshift, jidx;                             // chunk subsequences per tile = 1 << sshift (0 unless the items split the chunks); this warp's
     int stage_f4;                                 // float4 per ring stage (>= 3 * PIPE_CHUNK; the forward appends a zero record)
-    int pk, p_off;
+    int pk, p_off, p_cs;
     int2 p_rg, p_nx;
     uint32_t seq;                                 // chunks consumed so far
 
@@ -106,20 +107,32 @@ struct ChunkPipe {
         const int c = rg.y - rg.x;
         return make_int2(rg.x, c > 0 && rg.x != 0x7fffffff ? min(c, GI2D_BATCH) : 0);     // Q1: first 256 only
     }
+    // Records per chunk of a tile with n records.  Forward: always PIPE_CHUNK.  Backward (items split the chunks): the tile's
+    // records are cut into EQUAL chunks, their number a multiple of the items per tile -- with chunks of 64 a tile of 111
+    // records gave one warp 64 records and its partner 47, and since partners sit in CTAs of opposite parity, the SMs' shares
+    // of the records differed by +-25 % (tools/trace_raster.py).
+    __device__ __forceinline__ int chunk_size(int n) const {
+        if (sshift == 0) return PIPE_CHUNK;
+        int k = (n + PIPE_CHUNK - 1) / PIPE_CHUNK;
+        const int mask = (1 << sshift) - 1;
+        if (n > 32) k = (k + mask) & ~mask;
+        return k <= 1 ? n : k == 2 ? (n + 1) >> 1 : k == 3 ? ((n + 2) * 171) >> 9 : k == 4 ? (n + 3) >> 2 : (n + k - 1) / k;
+    }
     __device__ __forceinline__ void produce(int st) {
         while (pk < n_items && p_off >= p_rg.y) {          // item exhausted (or empty): move on
             pk += stride;
-            p_off = c_first;
             p_rg = p_nx;
+            p_cs = chunk_size(p_rg.y);
+            p_off = jidx * p_cs;
             p_nx = (pk + stride < n_items) ? load_range(pk + stride) : make_int2(0, 0);
         }
         if (pk >= n_items) return;
-        const uint32_t bytes = (uint32_t)min(PIPE_CHUNK, p_rg.y - p_off) * 48u;
+        const uint32_t bytes = (uint32_t)min(p_cs, p_rg.y - p_off) * 48u;
         if (lane == 0) {
             mbar_expect_tx(&bars[st], bytes);
             tma_load_1d(ring + (size_t)st * stage_f4, packed + 3 * (size_t)(p_rg.x + p_off), bytes, &bars[st]);
         }
-        p_off += c_step;
+        p_off += p_cs << sshift;
     }
     __device__ __forceinline__ void init(const int *tile_bins, const float4 *packed_, float4 *ring_, uint64_t *bars_, int tile_begin_,
                                          int n_tiles, int ishift_, bool split_chunks, int first, int stride_, int lane_, bool tma,
@@ -128,10 +141,11 @@ struct ChunkPipe {
         bins2 = reinterpret_cast<const int2 *>(tile_bins);
         packed = packed_; ring = ring_; bars = bars_;
         tile_begin = tile_begin_; ishift = ishift_; n_items = n_tiles << ishift_; stride = stride_; lane = lane_;
-        c_first = split_chunks ? (first & ((1 << ishift_) - 1)) * PIPE_CHUNK : 0;
-        c_step = split_chunks ? PIPE_CHUNK << ishift_ : PIPE_CHUNK;
-        pk = first; p_off = c_first; seq = 0;
+        sshift = split_chunks ? ishift_ : 0;
+        jidx = split_chunks ? (first & ((1 << ishift_) - 1)) : 0;
+        pk = first; seq = 0;
         p_rg = p_nx = make_int2(0, 0);
+        p_cs = PIPE_CHUNK; p_off = 0;
         if (!tma) return;
         if (lane == 0) {
 #pragma unroll
@@ -141,6 +155,8 @@ struct ChunkPipe {
         __syncwarp();
         if (pk < n_items) p_rg = load_range(pk);
         if (pk + stride < n_items) p_nx = load_range(pk + stride);
+        p_cs = chunk_size(p_rg.y);
+        p_off = jidx * p_cs;
 #pragma unroll
         for (int s = 0; s < PIPE_NST; ++s) produce(s);
     }
@@ -583,7 +599,8 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
         const int2 rg = c_nx;
         if (q + stride < n_items) c_nx = pipe.load_range(q + stride);
         const int lo = rg.x, cnt = rg.y;
-        if (cnt <= pipe.c_first) continue;                 // nothing for this item in the tile
+        const int cs = pipe.chunk_size(cnt);               // records per chunk of this tile (equal chunks)
+        if (cnt <= pipe.jidx * cs) continue;               // nothing for this item in the tile
         const int k = q >> ishift;
         const int ty = k / TX, tx = k - ty * TX;
         const int tx0 = tx * GI2D_TILE, ty0 = ty * GI2D_TILE;
@@ -612,8 +629,8 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
         }
         // (visibility of S.v4 to the other lanes: the __syncwarp after the prefix stores below)
 
-        for (int off = pipe.c_first; off < cnt; off += pipe.c_step) {
-            const int n = min(PIPE_CHUNK, cnt - off);
+        for (int off = pipe.jidx * cs; off < cnt; off += cs << pipe.sshift) {
+            const int n = min(cs, cnt - off);
             float4 *rec;
             if (TMA) {
                 rec = pipe.acquire();
