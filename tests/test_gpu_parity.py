@@ -322,6 +322,51 @@ def test_backward_vs_oracle_and_reference_kernel(name):
             assert_grad_close(_np(g), _np(r), f"{nm} vs reference kernel")
 
 
+@pytest.mark.parametrize("name", ["ragged", "c1_small", "dense"])
+def test_opacities_above_one_take_the_clamped_walk_and_match_oracle_and_reference(name):
+    """Both rasterizers compile the min(1, alpha) of forward.cu:601 / backward.cu:805 only into the walk of chunks that hold an
+    opacity > 1 (a warp vote per chunk); every other test runs the model's opacity == 1.  Mixed opacities in [0.2, 3): chunks
+    of both kinds, clamped alphas near every Gaussian's centre."""
+    s = scene(name)
+    N = s.means2d.shape[0]
+    g = torch.Generator().manual_seed(11)
+    s.opacity = (0.2 + 2.8 * torch.rand(N, 1, generator=g)) * (torch.rand(N, 1, generator=g) < 0.3) + \
+                torch.rand(N, 1, generator=g).clamp_min(0.05) * 1.0
+    s.opacity = s.opacity.clamp(0.05, 3.0).contiguous()
+    assert (s.opacity > 1).float().mean() > 0.1 and (s.opacity <= 1).float().mean() > 0.3
+    d = s.to(DEV)
+    _, st = oracle_chain(s)
+    f = _fused_internals(d, s)
+    assert np.array_equal(_np(f["gids_sorted"]), st["gaussian_ids_sorted"])
+    want, _, w_fidx, amb = O.rasterize_sum_forward(s.H, s.W, st["gaussian_ids_sorted"], st["tile_bins"], st["xys"], st["conics"],
+                                                 _np(s.colors), _np(s.opacity), want_ambig=True)
+    amb = amb.astype(bool)
+    assert_image_close(_np(f["out"]), want, "forward image, opacities up to 3", exclude=amb)
+    assert np.array_equal(_np(f["fidx"])[~amb], w_fidx[~amb])
+    gen = torch.Generator().manual_seed(3)
+    v_out = torch.randn(s.H, s.W, 3, generator=gen)
+    want_g = O.rasterize_sum_backward(s.H, s.W, st["gaussian_ids_sorted"], st["tile_bins"], st["xys"], st["conics"], _np(s.colors),
+                                      _np(s.opacity), st["final_idx"], v_out.numpy())
+    from gaussianimage_b200._lib import check, lib
+    (TX, TY, _) = s.tile_bounds
+    grads = torch.empty(N, 12, device=DEV)
+    v_out_d = v_out.to(DEV)
+    check(lib().gi2d_raster_sum_bwd_packed(N, TX, TY, s.W, s.H, f["tile_bins"].data_ptr(), f["packed"].data_ptr(), v_out_d.data_ptr(),
+                                           grads.data_ptr(), torch.cuda.current_stream().cuda_stream), "bwd packed")
+    got = (grads[:, 0:2], grads[:, 2:5], grads[:, 5:8], grads[:, 8:9])
+    for gg, w, nm in zip(got, want_g, ("v_xy", "v_conic", "v_colors", "v_opacity")):
+        assert_grad_close(_np(gg), w, f"{nm} (opacities up to 3) vs oracle")
+    if refcuda.available("jit"):
+        n, cum, ids, gids, ids_s, gids_s, bins = refcuda.bin_and_sort(f["xys"], f["depths"], f["radii"], f["nth"], s.H, s.W)
+        for flavor in ("jit", "fast"):
+            r_out, r_Ts, r_fidx = refcuda.rasterize_sum_fwd(s.H, s.W, gids_s, bins, f["xys"], f["conics"], d.colors, d.opacity, flavor)
+            assert torch.equal(f["out"], r_out), f"image differs from the reference kernel ({flavor}) with opacities > 1"
+            assert torch.equal(f["fidx"], r_fidx)
+        ref = refcuda.rasterize_sum_bwd(s.H, s.W, gids_s, bins, f["xys"], f["conics"], d.colors, d.opacity, f["Ts"], f["fidx"], v_out_d)
+        for gg, r, nm in zip(got, ref, ("v_xy", "v_conic", "v_colors", "v_opacity")):
+            assert_grad_close(_np(gg), _np(r), f"{nm} (opacities up to 3) vs reference kernel")
+
+
 def test_projection_backward_vs_oracle_and_reference_kernel():
     s = scene("c1_small")
     d = s.to(DEV)
