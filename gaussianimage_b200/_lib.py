@@ -143,7 +143,7 @@ _cpp_autograd = os.environ.get("GI2D_CPP_AUTOGRAD", "1") != "0"
 
 def cpp_autograd():
     """The glue module when the operators run as C++ autograd Functions with the fused chain's policy in C++
-    (csrc/torch_glue.cpp: ProjectFn, RasterFn, rasterize) -- the default whenever the glue is built -- else None:
+    (csrc/torch_glue.cpp: ProjectNode, RasterNode, rasterize) -- the default whenever the glue is built -- else None:
     GI2D_CPP_AUTOGRAD=0 / set_cpp_autograd(False) select the Python autograd Functions over the same kernels."""
     return glue() if _cpp_autograd else None
 

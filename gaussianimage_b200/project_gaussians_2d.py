@@ -43,7 +43,7 @@ def project_gaussians_2d(
     the reference kernel (quirk Q11).
     """
     T = cpp_autograd()
-    if T is not None:               # the same operator as a C++ autograd Function (csrc/torch_glue.cpp: ProjectFn)
+    if T is not None:               # the same operator as a C++ autograd node (csrc/torch_glue.cpp: ProjectNode)
         out = T.project_autograd(0, means2d.contiguous(), L_elements.contiguous(), None, img_height, img_width,
                                  tile_bounds[0], tile_bounds[1])
         _tag_zero_depth(out[1], out[0])

@@ -749,7 +749,7 @@ def test_ctypes_host_path_passes_the_operator_checks_without_the_glue():
 
 
 def test_cpp_autograd_functions_pass_the_operator_level_suite():
-    """The two operators as C++ autograd Functions (csrc/torch_glue.cpp: ProjectFn, RasterFusedFn; GI2D_CPP_AUTOGRAD=1):
+    """The two operators as C++ autograd nodes (csrc/torch_glue.cpp: ProjectNode, RasterNode; the default, GI2D_CPP_AUTOGRAD != 0):
     every operator-level parity test of this file, the caller-shaped tests, the loss-epilogue and the graph-fit tests re-run
     in a fresh interpreter with the switch set (and with GI2D_CPP_AUTOGRAD=0 when C++ is the default), so that BOTH
     autograd front ends are held to the same bar."""
