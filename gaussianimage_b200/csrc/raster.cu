@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
             GI2D_TRACE_WORK(n);
             // which records of the chunk touch this lane's pixel block: 64-bit mask from 2 x (NBX + NBY = 12) ballots
             uint32_t m[2] = {0u, 0u};
-            bool big = false;                              // a record whose opacity is not <= 1: alpha needs the min(1, .) of forward.cu:601
+            bool big = false;                              // a record that needs the careful walk: opacity not <= 1 (min(1, .) of forward.cu:601) ...
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if (h == 1 && n <= 32) break;              // sparse tiles (8K decode: ~19 records per tile): one round of ballots
@@ -329,9 +329,13 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                     const float4 A = rec[3 * t];
                     const float4 Bq = rec[3 * t + 1];
                     // ... or whose fields could make sigma NaN (non-finite, or large enough to overflow): min(1, NaN) = 1 there
+                    // ... or that carries no extent (+inf: visible_extent's guard D > 2e-3 cx cz, cx, cz > 0 failed).  With the guard,
+                    // sigma >= 1e-3 * (0.5 cx dx^2 + 0.5 cz dy^2), three orders above its fp32 rounding error: `sigma < 0` is
+                    // impossible and the fast walk does not test it.
+                    const float4 Cq = rec[3 * t + 2];
                     big = big || !(A.z <= 1.f) || !(fabsf(A.x) < 1e6f) || !(fabsf(A.y) < 1e6f) || !(fabsf(A.w) < 1e18f) ||
-                          !(fabsf(Bq.x) < 1e18f) || !(fabsf(Bq.y) < 1e18f);
-                    if (record_rect(A, rec[3 * t + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
+                          !(fabsf(Bq.x) < 1e18f) || !(fabsf(Bq.y) < 1e18f) || !(Cq.z < 3.0e38f);
+                    if (record_rect(A, Cq, tx0, ty0, lx0, lx1, ly0, ly1)) {
                         const int r0 = max(ly0, row0) - row0, r1 = min(ly1, row0 + ROWS - 1) - row0;
                         if (r0 <= r1) {
                             colbits = (2u << (lx1 >> XSH)) - (1u << (lx0 >> XSH));
@@ -390,7 +394,7 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
                             const float sigma = ffma(dy, w[c], ffma(dx[c], hu[c], ht3));    // eval_sigma, hoisted
                             const float ov = fmul(A.z, exp_neg(sigma));
                             const float alpha = CLAMP1 ? fminf(ov, 1.f) : ov;
-                            if (!(sigma < 0.f) && !(alpha < GI2D_ALPHA_MIN)) {              // forward.cu:602-604
+                            if ((!CLAMP1 || !(sigma < 0.f)) && !(alpha < GI2D_ALPHA_MIN)) { // forward.cu:602-604
                                 acc[r][c][0] = ffma(alpha, B.z, acc[r][c][0]);             // forward.cu:607-609
                                 acc[r][c][1] = ffma(alpha, B.w, acc[r][c][1]);
                                 acc[r][c][2] = ffma(alpha, cb, acc[r][c][2]);
@@ -652,7 +656,7 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                 if (t < n) {
                     const float4 A = rec[3 * t], Bq = rec[3 * t + 1];
                     big = big || !(A.z <= 1.f) || !(fabsf(A.x) < 1e6f) || !(fabsf(A.y) < 1e6f) || !(fabsf(A.w) < 1e18f) ||
-                          !(fabsf(Bq.x) < 1e18f) || !(fabsf(Bq.y) < 1e18f);
+                          !(fabsf(Bq.x) < 1e18f) || !(fabsf(Bq.y) < 1e18f) || !(rec[3 * t + 2].z < 3.0e38f);
                 }
                 if (t < n && record_rect(rec[3 * t], rec[3 * t + 2], tx0, ty0, lx0, lx1, ly0, ly1)) {
                     const int bx0 = lx0 >> 2, nbx = (lx1 >> 2) - bx0 + 1, by0 = ly0 >> 1, nby = (ly1 >> 1) - by0 + 1;
@@ -762,7 +766,7 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                                     const float vis = exp_neg(sigma);
                                     const float ov = fmul(opac, vis);
                                     const float raw = CLAMP1 ? fminf(ov, 1.f) : ov;
-                                    const bool valid = !(sigma < 0.f) && !(raw < GI2D_ALPHA_MIN);                               // backward.cu:806-808
+                                    const bool valid = (!CLAMP1 || !(sigma < 0.f)) && !(raw < GI2D_ALPHA_MIN);                  // backward.cu:806-808
                                     const float v_alpha = fmaf(cr, vr[j], fmaf(cg, vg[j], cb * vb[j]));                          // :818-820
                                     float m;
                                     if (CLAMP1) {
