@@ -693,7 +693,7 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                     float S_m = 0.f, S_x = 0.f, S_y = 0.f, S_xx = 0.f, S_xy = 0.f, S_yy = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f;
                     // current record (registers) and its block range
                     float x, y, opac, hcx, cy, hcz, cr, cg, cb;      // hcx, hcz: HALF the conic's diagonal (0.5 cx dx dx + 0.5 cz dy dy: exact)
-                    int bx0, nbx, by0, base, rec_end;
+                    int bx0, nbx, by0, base, rec_end, rmul;       // rmul: kk / nbx == (kk * rmul) >> 7 for kk < 128 (nbx in 1..4)
                     size_t gid;
                     auto load_record = [&]() {
                         const float4 A = rec[3 * t], B = rec[3 * t + 1];
@@ -702,6 +702,7 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                         x = A.x; y = A.y; opac = A.z; hcx = fmul(A.w, 0.5f); cy = B.x; hcz = fmul(B.y, 0.5f); cr = B.z; cg = B.w;
                         const uint32_t rect = S.rect[t];
                         bx0 = rect & 3; nbx = (rect >> 2) & 7; by0 = rect >> 5;
+                        rmul = nbx == 3 ? 43 : 128 >> (nbx >> 1);                       // 128, 64, 43, 32
                         base = (int)S.pref[t];
                         rec_end = (int)S.pref[t + 1];
                     };
@@ -740,7 +741,7 @@ __global__ void __launch_bounds__(BW_THREADS, 3) raster_bwd_kernel(int TX, int W
                                 load_record();
                             }
                             const int kk = u - base;
-                            const int rowb = nbx == 1 ? kk : nbx == 2 ? (kk >> 1) : nbx == 4 ? (kk >> 2) : ((kk * 43) >> 7);
+                            const int rowb = (kk * rmul) >> 7;
                             const int bx = bx0 + kk - rowb * nbx, ly0 = 2 * (by0 + rowb);
                             const float fx0 = (float)(tx0 + 4 * bx);
                             float dx[4], hu[4], cw[4];
