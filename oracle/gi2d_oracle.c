@@ -128,8 +128,10 @@ void gi2d_oracle_project_cholesky_fwd(int N, const float *means2d, const float *
  *   cov.y = tmp[0][1] = fma(p, u, q*v)
  *   cov.z = tmp[1][1] = fma(u, u, v*v)
  * sinf/cosf are libdevice on the GPU and libm here: not bit-reproducible (1-2 ulp), so tile lists
- * of this variant are compared exactly only GPU-vs-GPU (oracle/_ref) and with a mismatch budget
- * against this file. */
+ * of this variant are compared exactly GPU-vs-GPU (oracle/_ref), and against this file exactly
+ * OUTSIDE the set of Gaussians whose radius, evaluated in float64 (gi2d_oracle.py:
+ * scale_rot_radius_shadow), sits within 2e-5 of a ceil step -- the only place where 1-2 ulp of
+ * sin/cos can change an integer output. */
 void gi2d_oracle_project_scale_rot_fwd(int N, const float *means2d, const float *scales, const float *rot, int H, int W,
                                        int TX, int TY, float *xys, float *depths, int32_t *radii, float *conics,
                                        int32_t *num_tiles_hit) {

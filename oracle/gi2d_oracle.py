@@ -230,3 +230,22 @@ def fit_step_scale_rot(means2d, scales, rot, colors, opac, gt, H, W):
     v_xy, v_conic, v_col, v_op = rasterize_sum_backward(H, W, gids_s, bins, xys, conics, colors, opac, fidx, v_out)
     _, v_mean, v_scale, v_rot = project_gaussians_2d_scale_rot_backward(scales, rot, H, W, radii, conics, v_xy, v_conic)
     return loss, dict(v_means2d=v_mean, v_scale=v_scale, v_rot=v_rot, v_colors=v_col, v_opacity=v_op)
+
+
+def scale_rot_radius_shadow(scales, rot, rel_tol=2e-5):
+    """float64 SHADOW of the scale-rotation projection's radius (foward2d.cu:71-123 + helpers.cuh:45-68, the same
+    formulas as gi2d_oracle_project_scale_rot_fwd, evaluated in double): returns (rf, near) where rf is the radius BEFORE
+    the ceil and `near` flags the Gaussians whose rf lies within rel_tol of an integer.  sinf / cosf are libm here and
+    libdevice on the GPU (1-2 ulp apart), so the fp32 radius may legitimately differ between the two ONLY where the ceil is
+    that close to a step: tests compare the integer outputs exactly outside the flagged set."""
+    s = np.asarray(scales, np.float64).reshape(-1, 2)
+    th = np.asarray(rot, np.float64).reshape(-1)
+    cs, sn = np.cos(th), np.sin(th)
+    p, u, q, v = cs * s[:, 0], -(sn * s[:, 0]), sn * s[:, 1], cs * s[:, 1]
+    a, b, c = p * p + q * q, p * u + q * v, u * u + v * v
+    det = a * c - b * b
+    bh = 0.5 * (a + c)
+    disc = np.maximum(bh * bh - det, 0.1)
+    rf = 3.0 * np.sqrt(bh + np.sqrt(disc))
+    near = np.abs(rf - np.round(rf)) <= rel_tol * np.maximum(rf, 1.0)
+    return rf, near

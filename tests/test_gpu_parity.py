@@ -141,11 +141,18 @@ def test_project_scale_rot_vs_reference_kernel_and_oracle():
         for g, r, nm in zip(got, ref, ("xys", "depths", "radii", "conics", "num_tiles_hit")):
             assert torch.equal(g, r), f"{nm} differs from the reference JIT-flag build"
     want = O.project_gaussians_2d_scale_rot(_np(s.means2d), _np(s.scales), _np(s.rotation), s.H, s.W)
-    # libm vs libdevice sin/cos: floats to 1e-5, integer outputs may flip at ceil()/tile boundaries (rare)
+    # libm vs libdevice sin/cos (1-2 ulp): floats to 1e-5; the integer outputs may differ ONLY where the radius' ceil sits
+    # on a step -- the float64 shadow of the oracle flags those Gaussians, everything else must be equal
     np.testing.assert_allclose(_np(got[0]), want[0], rtol=1e-6)
     np.testing.assert_allclose(_np(got[3]), want[3], rtol=1e-5, atol=2e-6)   # conic.y is a cancelling difference
-    assert (_np(got[2]) != want[2]).mean() < 1e-3
-    assert (_np(got[4]) != want[4]).mean() < 1e-3
+    rf, near = O.scale_rot_radius_shadow(_np(s.scales), _np(s.rotation))
+    assert near.mean() < 2e-3, "the flagged set must stay small for the comparison to mean something"
+    r_diff = _np(got[2]) != want[2]
+    assert not (r_diff & ~near).any(), f"{(r_diff & ~near).sum()} radii differ away from a ceil step"
+    assert (np.abs(_np(got[2])[~near] - np.ceil(rf[~near])) == 0).all(), "radius != ceil of its float64 shadow"
+    n_diff = _np(got[4]) != want[4]
+    assert not (n_diff & ~r_diff).any(), "num_tiles_hit differs where the radius does not"
+    print(f"\n[scale-rot vs oracle] flagged {int(near.sum())} of {near.size}; radii differing inside the flagged set: {int(r_diff.sum())}")
 
 
 def test_compute_cov2d_bounds_golden_and_oracle():
