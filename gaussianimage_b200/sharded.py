@@ -50,7 +50,7 @@ class RowShardedRenderer:
     second render*() call after it; consume it on the stream it was rendered on (or synchronise with that stream)."""
 
     def __init__(self, H: int, W: int, device, group: Optional[dist.ProcessGroup] = None, emulate_world: int = 0,
-                 fused: bool = False, exchange: str = "multicast"):
+                 fused: bool = False, exchange: str = "multicast", ce_queues: int = 0):
         """exchange (fused mode): "multicast" = one NVLS `multimem.st` per 16 bytes from the rasterizer, replicated by the switch;
         "p2p" = plain stores from the rasterizer to the peer-mapped frame buffer of every other rank; "ce" = the rasterizer
         writes its band locally and the COPY ENGINES push it to every peer (peer-to-peer cudaMemcpyAsync on the side stream)
@@ -92,7 +92,13 @@ class RowShardedRenderer:
                                             for k in range(1, self.world)])
             self.fused = True
             self._side = torch.cuda.Stream(device=self.device)
-            self._side2 = torch.cuda.Stream(device=self.device)      # second copy queue of the copy-engine exchange
+            # Copy queues of the copy-engine exchange (the peers are dealt round-robin over them).  ONE by default: the copies of
+            # a queue run one after the other, so at every moment the copies of all ranks form a permutation (rank r -> r + k) and no
+            # destination takes two streams at once.  More queues break that: N=8 measured 555-563 us per frame with one queue,
+            # 570-614 with three, 930-1030 with two, four or seven (tools/ce_queues.py); N=4: 436-441 with one or two.
+            import os
+            nq = int(ce_queues or os.environ.get("GI2D_CE_QUEUES", "1"))
+            self._ce_extra = [torch.cuda.Stream(device=self.device) for _ in range(max(0, min(nq, self.world - 1) - 1))]
             self._done = [torch.cuda.Event(), torch.cuda.Event()]
             torch.cuda.synchronize(self.device)
             self._hdls[0].barrier(channel=0)            # every rank's buffers are zeroed before anybody's stores arrive
@@ -197,20 +203,26 @@ class RowShardedRenderer:
                 lo, hi = self.rank * self.band_rows, (self.rank + 1) * self.band_rows
                 mine = self.buffers[b][lo:hi]
                 peers = self._peer_bufs[b]
-                if len(peers) > 1:          # two copy queues, so that two copy engines keep the links busy back to back
+                nq = len(self._ce_extra) + 1
+                if nq > 1:                  # several copy queues, so that several copy engines keep the links busy back to back
                     go = torch.cuda.Event()
                     go.record(self._side)
-                    with torch.cuda.stream(self._side2):
-                        self._side2.wait_event(go)
-                        for peer in peers[1::2]:
-                            peer[lo:hi].copy_(mine, non_blocking=True)
-                        back = torch.cuda.Event()
-                        back.record(self._side2)
-                    for peer in peers[0::2]:
+                    backs = []
+                    for q, extra in enumerate(self._ce_extra, start=1):
+                        with torch.cuda.stream(extra):
+                            extra.wait_event(go)
+                            for peer in peers[q::nq]:
+                                peer[lo:hi].copy_(mine, non_blocking=True)
+                            back = torch.cuda.Event()
+                            back.record(extra)
+                            backs.append(back)
+                    for peer in peers[0::nq]:
                         peer[lo:hi].copy_(mine, non_blocking=True)
-                    self._side.wait_event(back)
+                    for back in backs:
+                        self._side.wait_event(back)
                 else:
-                    peers[0][lo:hi].copy_(mine, non_blocking=True)
+                    for peer in peers:
+                        peer[lo:hi].copy_(mine, non_blocking=True)
             self._hdls[b].barrier(channel=0)
             self._done[b].record(self._side)
 
