@@ -251,13 +251,15 @@ class FitStep:
                     self.eager()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
-        g = torch.cuda.CUDAGraph()
+        from gaussianimage_b200 import graphs as GR
+        g = GR.new_graph()
         with torch.cuda.graph(g):
             if render_only:
                 with torch.no_grad():
                     self.out = self.forward()
             else:
                 self.loss, self.grads = self.eager()
+        self.memsets_folded = GR.fold_memsets(g)     # small memset nodes (ATen's reduction semaphores) -> fill kernels, before instantiation
         self.graph = g
         return g
 
@@ -633,8 +635,10 @@ def run_b200(args):
     d2h_stream = torch.cuda.Stream()
     frame = [torch.zeros(H, W, 3, device=dev) for _ in range(2)] if render_only else None
 
+    from gaussianimage_b200 import graphs as GR
+
     def capture_e2e(b):
-        g = torch.cuda.CUDAGraph()
+        g = GR.new_graph()
         with torch.cuda.graph(g):
             cap = torch.cuda.current_stream()
             copy_stream.wait_stream(cap)
@@ -659,6 +663,7 @@ def run_b200(args):
                 keep = step.eager()                         # (loss, gradients): stay alive with the graph
                 host_out[b].copy_(keep[0].detach().view(1), non_blocking=True)   # D2H of the step's result
             cap.wait_stream(copy_stream)
+        GR.fold_memsets(g)
         return g, keep
 
     # Fit steps: U consecutive steps per replayed graph (each with its own H2D of its inputs, its own conversion, its own D2H
@@ -678,7 +683,7 @@ def run_b200(args):
         """Critical path of the replayed graph = the U steps only.  Step u reads gt_pair[u & 1].  Beside it, on other branches:
         the H2D of step u+2's 8-bit target into stage4[(u + 2) % 4], the conversion of step u+1's (already arrived) target to
         fp32 into gt_pair[(u + 1) & 1] once step u-1 no longer reads that buffer, and the D2H of step u-1's loss."""
-        g = torch.cuda.CUDAGraph()
+        g = GR.new_graph()
         keep = []
         gt0 = step.gt
         with torch.cuda.graph(g):
@@ -702,6 +707,7 @@ def run_b200(args):
                 conv_stream.wait_stream(h2d_stream)         # ... and the conversion for step u+2 needs its bytes
             cap.wait_stream(d2h_stream)
             cap.wait_stream(h2d_stream)
+        GR.fold_memsets(g)
         step.gt = gt0
         return g, keep
 
@@ -935,6 +941,8 @@ def run_b200(args):
         "config": {"workload": workload_string(name, param, args.workload, W, H, N),
                    "l2": "256 MiB buffer rewritten between timed steps (flush)", "parallelism": f"image-parallel x{world}, no collective",
                    "peaks": peaks_src},
+        "graph": {"what": "CUDA-graph replay of the public-API step (projection, rasterization, F.mse_loss, autograd backward)",
+                  "memset_nodes_replaced_by_fill_kernels": getattr(step, "memsets_folded", 0)},
         "workload_stats": {"tile_intersections": counts["n_isect"], "pair_evaluations_algorithmic": counts["E"],
                            "pair_evaluations_executed": counts["E_eval"]},
         "ms_per_step_spread": spread(ts),

@@ -19,6 +19,7 @@ _vp, _i, _sz = C.c_void_p, C.c_int, C.c_size_t
 _SIGNATURES = {
     "gi2d_abi_version": (_i, []),
     "gi2d_status_string": (C.c_char_p, [_i]),
+    "gi2d_graph_fold_memsets": (_i, [_vp, _sz, _vp]),
     "gi2d_project_cholesky_fwd": (_i, [_i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_decode_project_cholesky_fwd": (_i, [_i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gi2d_project_scale_rot_fwd": (_i, [_i, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

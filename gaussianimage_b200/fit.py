@@ -106,9 +106,11 @@ class GraphFitter:
             self.iteration += 1
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
-        g = torch.cuda.CUDAGraph()
+        from . import graphs as GR
+        g = GR.new_graph()
         with torch.cuda.graph(g):
             self.step()
+        GR.fold_memsets(g)              # memset nodes (none on the fused path; ATen's reduction semaphores otherwise) -> fill kernels
         self.graph = g
         return g
 

@@ -43,6 +43,14 @@ int gi2d_abi_version(void);
 /* Static description of a status code returned by any function below. */
 const char *gi2d_status_string(int status);
 
+/* Helper for callers that replay a captured CUDA graph of a whole iteration (no counterpart in the reference, whose trainer
+ * runs eagerly): replaces every small 1-D MEMSET node of `graph` (a cudaGraph_t; height 1, element size 1/2/4, at most
+ * max_bytes) by a kernel node that writes the same bytes, with the node's dependencies and dependents.  Memset nodes between
+ * kernel nodes -- e.g. the semaphore clear in front of ATen's reduction kernels, which F.mse_loss records -- cost several
+ * microseconds of idle time on either side in a replay; a fill kernel does not.  The graph must not have been instantiated
+ * yet (torch: CUDAGraph(keep_graph=True), raw_cuda_graph(), then instantiate()).  *n_replaced = nodes replaced. */
+int gi2d_graph_fold_memsets(void *graph, size_t max_bytes, int *n_replaced);
+
 /* ---- projection ------------------------------------------------------------------------------------------- */
 
 /* Replaces project_gaussians_2d_forward (ext.cpp:16 -> bindings.cu:781-839 -> foward2d.cu:12-69).

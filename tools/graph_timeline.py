@@ -31,9 +31,11 @@ with torch.cuda.stream(side):
     for _ in range(3):
         step()
 torch.cuda.synchronize()
-g = torch.cuda.CUDAGraph()
+from gaussianimage_b200 import graphs as GR
+g = GR.new_graph()
 with torch.cuda.graph(g):
     keep = step()
+print("memset nodes replaced by fill kernels:", GR.fold_memsets(g))
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
 for _ in range(5):
     g.replay()
