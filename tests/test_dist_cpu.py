@@ -46,7 +46,7 @@ def test_row_sharded_gather_world2_matches_single_process():
     procs = [ctx.Process(target=_worker, args=(r, world, port, 70, 100, 300, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=120) for _ in range(world)]
+    res = [q.get(timeout=600) for _ in range(world)]       # generous: the driver may run this beside a build on a loaded box
     for p in procs:
         p.join(timeout=60)
     assert all(p.exitcode == 0 for p in procs)
