@@ -225,6 +225,7 @@ struct PeerOut {
 struct LossArgs {
     const float *gt;          // target, (3,H,W) planes when gt_chw else (H,W,3)
     int gt_chw, clamp;
+    int gt_vec;               // gt may be read with 16-byte loads (aligned base, W % 4 == 0)
     float inv_numel;          // 1 / (3 H W)
     float *v_out;             // (H,W,3): d loss / d out_img
     float *image;             // optional (H,W,3): the clamped image
@@ -422,32 +423,86 @@ __global__ void __launch_bounds__(FW_THREADS, 3) raster_fwd_kernel(int TX, int W
         float *const dst_img = LOSS ? la.v_out : out_img;
         const bool vec_tile = vec_ok && tx0 + GI2D_TILE <= W && ty0 + GI2D_TILE <= H;     // uniform over the warp
         constexpr bool staged = EXCH;
+        // LOSS: the target's values for the lane's BW pixels of a row are loaded together BEFORE their first use (as 16- / 8-byte
+        // loads on full tiles): element by element between the arithmetic they were a chain of 24 dependent L2 round trips at
+        // the end of every tile -- 4.5 us per tile, and at the fitting sizes a warp's tile IS the kernel's critical path.
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
             const int i = ty0 + row0 + 2 * bym + r, j0 = tx0 + BW * bxm;
             const size_t pix0 = (size_t)i * W + j0;
+            float gtv[LOSS ? 3 * BW : 1];
+            if (LOSS) {
+                const size_t plane = (size_t)H * W;
+                if (vec_tile && la.gt_vec) {
+                    if (la.gt_chw) {
+#pragma unroll
+                        for (int ch = 0; ch < 3; ++ch) {
+                            if (BW == 4) {
+                                const float4 g = __ldg(reinterpret_cast<const float4 *>(la.gt + ch * plane + pix0));
+                                gtv[ch] = g.x; gtv[3 + ch] = g.y; gtv[(6 + ch) % (3 * BW)] = g.z; gtv[(9 + ch) % (3 * BW)] = g.w;
+                            } else {
+                                const float2 g = __ldg(reinterpret_cast<const float2 *>(la.gt + ch * plane + pix0));
+                                gtv[ch] = g.x; gtv[3 + ch] = g.y;
+                            }
+                        }
+                    } else {
+                        if (BW == 4) {
+#pragma unroll
+                            for (int k4 = 0; k4 < 3; ++k4) {
+                                const float4 g = __ldg(reinterpret_cast<const float4 *>(la.gt + 3 * pix0) + k4);
+                                gtv[(4 * k4) % (3 * BW)] = g.x; gtv[(4 * k4 + 1) % (3 * BW)] = g.y;
+                                gtv[(4 * k4 + 2) % (3 * BW)] = g.z; gtv[(4 * k4 + 3) % (3 * BW)] = g.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int k2 = 0; k2 < 3; ++k2) {
+                                const float2 g = __ldg(reinterpret_cast<const float2 *>(la.gt + 3 * pix0) + k2);
+                                gtv[2 * k2] = g.x; gtv[2 * k2 + 1] = g.y;
+                            }
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < BW; ++c)
+#pragma unroll
+                        for (int ch = 0; ch < 3; ++ch) {
+                            const bool inside = i < H && j0 + c < W;
+                            const float *ptr = la.gt_chw ? la.gt + ch * plane + pix0 + c : la.gt + 3 * (pix0 + c) + ch;
+                            gtv[3 * c + ch] = inside ? __ldg(ptr) : 0.f;
+                        }
+                }
+            }
             float v[3 * BW];
 #pragma unroll
             for (int c = 0; c < BW; ++c) { v[3 * c] = acc[r][c][0]; v[3 * c + 1] = acc[r][c][1]; v[3 * c + 2] = acc[r][c][2]; }
             if (LOSS) {
                 const float sc = 2.f * la.inv_numel;
-                const size_t plane = (size_t)H * W;
+                float cl[3 * BW];
 #pragma unroll
                 for (int c = 0; c < BW; ++c) {
                     const bool inside = i < H && j0 + c < W;
 #pragma unroll
                     for (int ch = 0; ch < 3; ++ch) {
                         const float raw = v[3 * c + ch];
-                        const float cl = la.clamp ? fminf(fmaxf(raw, 0.f), 1.f) : raw;
-                        float d = 0.f;
-                        if (inside) {
-                            const float g = la.gt_chw ? __ldg(la.gt + ch * plane + pix0 + c) : __ldg(la.gt + 3 * (pix0 + c) + ch);
-                            d = cl - g;
-                            if (la.image) la.image[3 * (pix0 + c) + ch] = cl;
-                        }
+                        cl[3 * c + ch] = la.clamp ? fminf(fmaxf(raw, 0.f), 1.f) : raw;
+                        const float d = inside ? cl[3 * c + ch] - gtv[3 * c + ch] : 0.f;
                         sq_sum += d * d;
                         // torch.clamp passes the gradient where min <= x <= max
                         v[3 * c + ch] = (!la.clamp || (raw >= 0.f && raw <= 1.f)) ? sc * d : 0.f;
+                    }
+                }
+                if (la.image) {                             // the clamped image (optional output)
+                    if (vec_tile && la.gt_vec && BW == 4) {
+#pragma unroll
+                        for (int k4 = 0; k4 < 3; ++k4)
+                            *reinterpret_cast<float4 *>(la.image + 3 * pix0 + 4 * k4) = make_float4(cl[4 * k4], cl[4 * k4 + 1], cl[4 * k4 + 2], cl[4 * k4 + 3]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BW; ++c)
+                            if (i < H && j0 + c < W) {
+#pragma unroll
+                                for (int ch = 0; ch < 3; ++ch) la.image[3 * (pix0 + c) + ch] = cl[3 * c + ch];
+                            }
                     }
                 }
             }
@@ -1036,7 +1091,7 @@ int gi2d_raster_sum_fwd_packed_mse(int TX, int TY, int W, int H, int *tile_bins,
     const int nt = TX * TY;
     const int grid = fwd_grid_for<true, false, true>(nt);
     if (ws_bytes < sizeof(float) * (size_t)grid + 16) return GI2D_ERR_WORKSPACE;
-    LossArgs la{gt, gt_is_chw ? 1 : 0, clamp01 ? 1 : 0, 1.f / (3.f * (float)H * (float)W), v_out, image,
+    LossArgs la{gt, gt_is_chw ? 1 : 0, clamp01 ? 1 : 0, vec_ok(W, gt) && vec_ok(W, image), 1.f / (3.f * (float)H * (float)W), v_out, image,
                 reinterpret_cast<float *>(reinterpret_cast<char *>(ws) + 16), reinterpret_cast<unsigned int *>(ws), loss};
     GatherSrc src{nullptr, nullptr, nullptr, nullptr, nullptr};
     const FwdArgs a{TX, W, H, 0, nt, tile_bins, reinterpret_cast<const float4 *>(packed), src, d_status, background, nullptr, nullptr, nullptr,

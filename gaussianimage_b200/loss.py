@@ -67,8 +67,13 @@ class _RasterizeSumMSE(Function):
             r.extra = (v_out, image, loss)
 
         bg = _default_background(colors) if background is None else _C._f32(background.to(dev).contiguous(), "background")
-        r = _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, bg, False, raster)
+        # the (N,12) gradient rows of the backward pass are allocated here and zero-filled by the binning chain (which touches
+        # every Gaussian anyway): no memset in front of the backward rasterizer
+        want_grads = any(ctx.needs_input_grad[k] for k in (0, 3, 5, 6))          # xys, conics, colors, opacity
+        grads = torch.empty((xys.size(0), 12), dtype=torch.float32, device=dev) if want_grads else None
+        r = _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, bg, False, raster, zero_g12=grads)
         v_out, image, loss = r.extra
+        ctx.fresh_grads = grads
         ctx.save_for_backward(r.tile_bins, r.packed, v_out)
         if return_image:
             ctx.mark_non_differentiable(image)
@@ -84,10 +89,16 @@ class _RasterizeSumMSE(Function):
         dev = packed.device
         scale = _C._f32(v_loss.contiguous(), "v_loss")
         with _C._guard(dev):
-            grads = torch.empty((N, 12), dtype=torch.float32, device=dev)
-            check(lib().gi2d_raster_sum_bwd_packed_scaled(N, TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(), v_out.data_ptr(),
-                                                          scale.data_ptr(), grads.data_ptr(), _C._stream(dev)),
-                  "rasterize_sum_backward")
+            grads, ctx.fresh_grads = getattr(ctx, "fresh_grads", None), None       # zeroed by the forward's chain: one use only
+            if grads is not None:
+                check(lib().gi2d_raster_sum_bwd_packed_acc(N, TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(), v_out.data_ptr(),
+                                                           scale.data_ptr(), grads.data_ptr(), _C._stream(dev)),
+                      "rasterize_sum_backward")
+            else:                                   # a second backward through the same node: rows allocated and zeroed here
+                grads = torch.empty((N, 12), dtype=torch.float32, device=dev)
+                check(lib().gi2d_raster_sum_bwd_packed_scaled(N, TX, TY, W, H, tile_bins.data_ptr(), packed.data_ptr(), v_out.data_ptr(),
+                                                              scale.data_ptr(), grads.data_ptr(), _C._stream(dev)),
+                      "rasterize_sum_backward")
         v_opacity = grads[:, 8:9].reshape(ctx.opacity_shape)
         return (grads[:, 0:2], None, None, grads[:, 2:5], None, grads[:, 5:8], v_opacity, None, None, None, None, None, None)
 

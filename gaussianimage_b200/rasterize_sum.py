@@ -284,7 +284,7 @@ class FusedResult:
 
 
 def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, H, W, cap, want_aux=False, host_slot=-1,
-                raster=None, sticky=None):
+                raster=None, sticky=None, zero_g12=None):
     """One asynchronous pass of the fused chain (csrc/binning.cu gi2d_bin_fused + csrc/raster.cu packed forward) on the
     current stream with an intersection capacity `cap`.  Returns a FusedResult: out_img, final_Ts/final_idx (or None),
     tile_bins (T,2), packed (cap*12), gids_sorted (cap), status (2,) = [n, overflow].  host_slot >= 0 also publishes the
@@ -315,7 +315,8 @@ def fused_chain(xys, radii, conics, num_tiles_hit, colors, opacity, background, 
     host_ptr = _host_status.base + 8 * host_slot if host_slot >= 0 else 0
     a = BinArgs(N, TX, TY, 0, TY, cap, xys.data_ptr(), radii.data_ptr(), num_tiles_hit.data_ptr(), conics.data_ptr(),
                 colors.data_ptr(), opacity.data_ptr(), base, ws_bytes, base + o_gids, tile_bins.data_ptr(), packed.data_ptr(),
-                base + o_status, host_ptr or None, None if sticky is None else sticky.data_ptr(), None)
+                base + o_status, host_ptr or None, None if sticky is None else sticky.data_ptr(),
+                None if zero_g12 is None else zero_g12.data_ptr())      # zero_g12: (N,12) gradient rows the chain zero-fills
     check(L.gi2d_bin_fused_ex(C.byref(a), stream), "bin_fused")
     if raster is not None:                 # another consumer of the lists (loss.py: forward that ends in the loss)
         r.out_img = r.final_Ts = r.final_idx = None
@@ -372,7 +373,7 @@ def set_memoise_binning(flag: bool):
         T.set_memoise(_memoise)
 
 
-def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=False, raster=None):
+def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=False, raster=None, zero_g12=None):
     """Rasterize the geometry of a previous fused_chain result with other conics / colours / opacities."""
     dev = xys.device
     L = lib()
@@ -384,8 +385,9 @@ def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=F
     r.tile_bins = src.tile_bins
     r.packed = packed = torch.empty((cap * 12,), dtype=torch.float32, device=dev)
     base = src._scratch.data_ptr()
-    check(L.gi2d_repack_records(cap, base + src._o_gids, base + src._o_status, xys.data_ptr(), conics.data_ptr(),
-                                colors.data_ptr(), opacity.data_ptr(), packed.data_ptr(), stream), "repack_records")
+    check(L.gi2d_repack_records_ex(cap, base + src._o_gids, base + src._o_status, xys.data_ptr(), conics.data_ptr(),
+                                   colors.data_ptr(), opacity.data_ptr(), packed.data_ptr(), xys.size(0),
+                                   None if zero_g12 is None else zero_g12.data_ptr(), stream), "repack_records")
     if raster is not None:
         r.out_img = r.final_Ts = r.final_idx = None
         raster(r, base + src._o_status, stream)
@@ -399,7 +401,7 @@ def fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux=F
     return r
 
 
-def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background, want_aux, raster=None):
+def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, background, want_aux, raster=None, zero_g12=None):
     global _host_status, geometry_hits
     N, H, W, TX, TY = ctx.N, ctx.H, ctx.W, ctx.TX, ctx.TY
     dev = xys.device
@@ -423,7 +425,7 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
             g = None
         if g is not None and g.matches(xys, radii, nth, key):
             geometry_hits += 1
-            r = fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux, raster)
+            r = fused_reraster(g, xys, conics, colors, opacity, background, H, W, want_aux, raster, zero_g12)
             if g.n_isect is not None:
                 ctx.num_intersects = g.n_isect
             if raster is not None:
@@ -436,7 +438,7 @@ def _forward_fused(ctx, xys, radii, conics, num_tiles_hit, colors, opacity, back
                 cap = _capacity[key] = max(4 * N, 1 << 14)
             slot = _host_status.acquire() if strict else -1
             r = fused_chain(xys, radii, conics, nth, colors, opacity, background, H, W, cap, want_aux, slot, raster,
-                            None if strict else sticky)
+                            None if strict else sticky, zero_g12)
             _last_status[dev.index] = (r._scratch, r._o_status, cap, key)
             n = None
             if not strict:

@@ -29,6 +29,8 @@ L.gi2d_bin_fused.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, i32, vp, sz,
 L.gi2d_raster_sum_fwd_packed.argtypes = [i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
 L.gi2d_raster_sum_bwd_packed.argtypes = [i32, i32, i32, i32, i32, vp, vp, vp, vp, vp]
 L.gi2d_debug_set_trace.argtypes = [vp]
+L.gi2d_raster_mse_workspace_bytes.restype = sz
+L.gi2d_raster_sum_fwd_packed_mse.argtypes = [i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, sz, vp]
 
 args = [a for a in sys.argv[1:] if not a.startswith("--")]
 cfg = args[0] if args else "C2"
@@ -68,6 +70,17 @@ def fwd():
                                         out.data_ptr(), 0, 0, st) == 0
 
 
+mse_ws = torch.zeros(max(int(L.gi2d_raster_mse_workspace_bytes()), 4), dtype=torch.uint8, device=dev)
+gt_chw = d.gt.permute(2, 0, 1).contiguous()
+loss = torch.zeros(1, device=dev)
+
+
+def fwd_loss():
+    assert L.gi2d_raster_sum_fwd_packed_mse(TX, TY, W, H, bins.data_ptr(), packed.data_ptr(), status.data_ptr(), bg.data_ptr(),
+                                            gt_chw.data_ptr(), 1, 1, v_out.data_ptr(), 0, loss.data_ptr(), mse_ws.data_ptr(),
+                                            mse_ws.numel(), st) == 0
+
+
 def bwd():
     assert L.gi2d_raster_sum_bwd_packed(N, TX, TY, W, H, bins.data_ptr(), packed.data_ptr(), v_out.data_ptr(), grads.data_ptr(), st) == 0
 
@@ -78,7 +91,7 @@ def pct(a, qs=(0, 10, 50, 90, 100)):
 
 GHZ = 1.965                                               # SM clock under load on this pool (bench.py's clocks line)
 for warm in (True, False):
-    for name, fn in (("raster_fwd", fwd), ("raster_bwd", bwd)):
+    for name, fn in (("raster_fwd", fwd), ("raster_fwd_loss", fwd_loss), ("raster_bwd", bwd)):
         for _ in range(3):
             binning(); fn()
         if warm:
